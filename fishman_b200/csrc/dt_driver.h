@@ -1,0 +1,195 @@
+// dt_driver.h -- host-side control of the Delaunay rounds, written once against
+// a small "backend" concept so that the CUDA library (fishman_b200.cu) and the
+// CPU logic tests (tests/emu) run the SAME round structure:
+//
+//   Backend::launch<K>(ctx, n)            run body K for thread ids [0, n)
+//   Backend::fill64(ptr, value, count)    device memset of 64-bit words
+//   Backend::fill32(ptr, value, count)
+//   Backend::exclusive_scan(ptr, n)       in place over ints; returns the total
+//   Backend::read_ints(dst, src, n)       device -> host (synchronising)
+//   Backend::write_ints(dst, src, n)      host -> device
+//   Backend::argmax_dot(ctx, d)           index of the point with the largest p . d
+//   Backend::fetch_point(ctx, i)          coordinates of point i on the host
+//   Backend::fetch_orig(ctx, i)
+//   Backend::write_tris(ctx, t0, cnt, tri, adj)
+//
+// Replaces: the bootstrap get_three_DVT_indices / init_DTs
+// (/root/reference/src/delaunay_voronoi_mod.F90:595-694) and the loop structure
+// of delaunay_triangulation (DV:226-356).  The reference starts from three random
+// points plus three VIRTUAL antipodal vertices that it must delete again at the
+// end (DV:772-843); this driver starts from four REAL points whose tetrahedron
+// contains the origin, so there is nothing to delete and the triangle count is
+// 2N-4 from the first round on.
+#pragma once
+#include <stdio.h>
+#include <string.h>
+
+#include "dt_kernels.cuh"
+
+namespace fm {
+
+struct DtStats {
+  int rounds, subrounds, flips, max_active;
+  long long located;
+};
+
+// Chooses the four bootstrap points and writes the four faces.  Returns 0, or 1
+// with msg filled when the points do not surround the origin.
+template <class B>
+int dt_bootstrap(B& be, DtCtx& c, int boot[4], char* msg, size_t msglen) {
+  static const double dirs[4][3] = {{1, 1, 1}, {1, -1, -1}, {-1, 1, -1}, {-1, -1, 1}};
+  static const int F[4][3] = {{0, 1, 2}, {0, 3, 1}, {1, 3, 2}, {0, 2, 3}};
+  P3 p[4];
+  int id[4];
+  bool ok = false;
+  // attempts 0..7: the extreme points along the axes of a regular tetrahedron,
+  // first axis-aligned, then in seven fixed pseudo-random rotations (symmetric
+  // sets tie along special axes); attempt 8: a, the point most opposite to a,
+  // the point farthest from their great circle, the point most opposite to all.
+  const int kLast = 8;
+  unsigned long long lcg = 0x9E3779B97F4A7C15ULL;
+  for (int attempt = 0; attempt <= kLast && !ok; attempt++) {
+    bool distinct = true;
+    double R[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    if (attempt > 0 && attempt < kLast) {
+      double q[4], nq = 0;
+      for (int j = 0; j < 4; j++) {
+        lcg = lcg * 6364136223846793005ULL + 1442695040888963407ULL;
+        q[j] = (double)((lcg >> 11) & 0xfffff) / 524288.0 - 1.0;
+        nq += q[j] * q[j];
+      }
+      nq = sqrt(nq) + 1e-300;
+      double w = q[0] / nq, x = q[1] / nq, y = q[2] / nq, z = q[3] / nq;
+      R[0][0] = 1 - 2 * (y * y + z * z); R[0][1] = 2 * (x * y - z * w); R[0][2] = 2 * (x * z + y * w);
+      R[1][0] = 2 * (x * y + z * w); R[1][1] = 1 - 2 * (x * x + z * z); R[1][2] = 2 * (y * z - x * w);
+      R[2][0] = 2 * (x * z - y * w); R[2][1] = 2 * (y * z + x * w); R[2][2] = 1 - 2 * (x * x + y * y);
+    }
+    for (int k = 0; k < 4; k++) {
+      double d[3];
+      if (attempt < kLast || k == 0) {
+        for (int r = 0; r < 3; r++)
+          d[r] = R[r][0] * dirs[k][0] + R[r][1] * dirs[k][1] + R[r][2] * dirs[k][2];
+      } else if (k == 1) {
+        d[0] = -p[0].x; d[1] = -p[0].y; d[2] = -p[0].z;
+      } else if (k == 2) {
+        d[0] = p[0].y * p[1].z - p[0].z * p[1].y;
+        d[1] = p[0].z * p[1].x - p[0].x * p[1].z;
+        d[2] = p[0].x * p[1].y - p[0].y * p[1].x;
+        if (d[0] == 0.0 && d[1] == 0.0 && d[2] == 0.0) { d[0] = p[0].y; d[1] = p[0].z; d[2] = p[0].x; }
+      } else {
+        d[0] = -(p[0].x + p[1].x + p[2].x); d[1] = -(p[0].y + p[1].y + p[2].y);
+        d[2] = -(p[0].z + p[1].z + p[2].z);
+      }
+      boot[k] = be.argmax_dot(c, d);
+      if (attempt == kLast && k == 2) {  // the far side of the great circle may hold the better point
+        double nd[3] = {-d[0], -d[1], -d[2]};
+        int alt = be.argmax_dot(c, nd);
+        P3 q1 = be.fetch_point(c, boot[k]), q2 = be.fetch_point(c, alt);
+        double v1 = q1.x * d[0] + q1.y * d[1] + q1.z * d[2];
+        double v2 = q2.x * nd[0] + q2.y * nd[1] + q2.z * nd[2];
+        if (v2 > v1) boot[k] = alt;
+      }
+      p[k] = be.fetch_point(c, boot[k]);
+      id[k] = be.fetch_orig(c, boot[k]);
+      for (int j = 0; j < k; j++)
+        if (boot[j] == boot[k]) distinct = false;
+    }
+    if (!distinct) continue;
+    if (orient(p[0], p[1], p[2], id[0], id[1], id[2]) < 0) {
+      int tb = boot[1]; boot[1] = boot[2]; boot[2] = tb;
+      P3 tp = p[1]; p[1] = p[2]; p[2] = tp;
+      int ti = id[1]; id[1] = id[2]; id[2] = ti;
+    }
+    // closed, consistently oriented surface of the tetrahedron (p0,p1,p2,p3):
+    // the origin is strictly inside iff every face is CCW seen from outside
+    ok = true;
+    for (int f = 0; f < 4; f++) {
+      int a = F[f][0], b = F[f][1], d = F[f][2];
+      if (orient(p[a], p[b], p[d], id[a], id[b], id[d]) <= 0) ok = false;
+    }
+  }
+  if (!ok) {
+    snprintf(msg, msglen,
+             "bootstrap: no four points enclosing the sphere centre were found (points confined "
+             "to a hemisphere?)");
+    return 1;
+  }
+  I4 tri[4], adj[4];
+  for (int f = 0; f < 4; f++) tri[f] = I4{boot[F[f][0]], boot[F[f][1]], boot[F[f][2]], 0};
+  for (int f = 0; f < 4; f++) {
+    int a[3] = {-1, -1, -1};
+    for (int k = 0; k < 3; k++) {
+      int u = F[f][(k + 1) % 3], v = F[f][(k + 2) % 3];  // edge opposite vertex k
+      for (int g = 0; g < 4; g++)
+        for (int e = 0; e < 3; e++)
+          if (F[g][(e + 1) % 3] == v && F[g][(e + 2) % 3] == u) a[k] = enc(g, e);
+    }
+    adj[f] = I4{a[0], a[1], a[2], 0};
+  }
+  be.write_tris(c, 0, 4, tri, adj);
+  return 0;
+}
+
+// Runs insertion rounds until every point is a vertex.  Preconditions: the four
+// bootstrap faces are in slots 0..3, loc[] is 0 for every point but the
+// bootstrap ones (-1), vote[] is all ones, role/amark/mailbox are zero.
+// listA/listB: two int queues of max_tri entries.
+template <class B>
+int dt_run(B& be, DtCtx& c, int* listA, int* listB, DtStats* st, char* msg, size_t msglen) {
+  int remaining = c.n - 4;
+  int stamp = 1;
+  c.n_tri = 4;
+  memset(st, 0, sizeof *st);
+  int zero[4] = {0, 0, 0, 0}, host[4];
+  be.write_ints(c.counters, zero, 4);
+  while (remaining > 0) {
+    st->rounds++;
+    be.fill64(c.winner, kNone64, (size_t)c.n_tri);
+    be.template launch<KLocateVote>(c, c.n);
+    be.template launch<KSplitFlag>(c, c.n_tri);
+    int nsplit = be.exclusive_scan(c.rank, c.n_tri);
+    be.read_ints(host, c.err, 1);
+    if (host[0]) {
+      snprintf(msg, msglen, "point location failed (error bits %d): duplicate points?", host[0]);
+      return 1;
+    }
+    if (nsplit <= 0) {
+      snprintf(msg, msglen, "no triangle accepted a point although %d remain", remaining);
+      return 1;
+    }
+    be.write_ints(c.counters, zero, 1);
+    c.stamp = stamp;
+    c.next_active = listA;
+    be.template launch<KSplit>(c, c.n_tri);
+    remaining -= nsplit;
+    c.n_tri += 2 * nsplit;
+    int nact = 3 * nsplit;
+    int* cur = listA;
+    int* nxt = listB;
+    while (nact > 0) {
+      st->subrounds++;
+      if (nact > st->max_active) st->max_active = nact;
+      be.write_ints(c.counters, zero, 1);
+      c.stamp = stamp;
+      c.active = cur;
+      c.n_active = nact;
+      c.next_active = nxt;
+      be.template launch<KCheck>(c, nact);
+      be.template launch<KMark>(c, nact);
+      be.template launch<KFlip>(c, nact);
+      be.template launch<KPatch>(c, nact);
+      be.read_ints(host, c.counters, 4);
+      nact = host[0];
+      st->flips = host[2];
+      stamp++;
+      int* tmp = cur; cur = nxt; nxt = tmp;
+      if (stamp > (1 << 28)) {
+        snprintf(msg, msglen, "flip rounds did not terminate");
+        return 1;
+      }
+    }
+  }
+  return 0;
+}
+
+}  // namespace fm

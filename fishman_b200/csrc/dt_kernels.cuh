@@ -1,0 +1,319 @@
+// dt_kernels.cuh -- per-thread bodies of the Delaunay kernels.
+//
+// What they replace in the reference (/root/reference/src/delaunay_voronoi_mod.F90,
+// "DV"): the serial insertion loop DV:296-321 with its point-in-triangle buckets
+// (DV:247-293, DV:884-948), the 1->3 split flip13 (DV:957-1004) and the Lawson
+// legalisation validate_DT/flip22 (DV:845-882, DV:1098-1149).  The reference
+// inserts one point at a time in index order and re-buckets the points of every
+// destroyed triangle; here every triangle that still contains uninserted points
+// takes ONE of them per round (chosen by a 64-bit atomicMin), all winners are
+// split at once, and the mesh is brought back to Delaunay by rounds of
+// conflict-free 2<->2 flips (pairs claimed by atomicMin votes).  Points are not
+// kept in buckets: each uninserted point remembers the triangle SLOT it was last
+// in and re-locates itself by a short visibility walk (slots are rewritten in
+// place by splits and flips, so the walk starts next to the answer).
+//
+// Every body is a plain function of (context, thread id) that communicates only
+// through atomicMin / atomicAdd / atomicExch and stamped words, so the same
+// source runs (a) as the CUDA kernels of the product library and (b) thread by
+// thread on the host in tests/emu (CPU logic tests only; never shipped).
+#pragma once
+#include "predicates.cuh"
+
+namespace fm {
+
+struct alignas(16) I4 {
+  int x, y, z, w;
+};
+
+#if defined(__CUDA_ARCH__)
+#define FM_ATOMIC_MIN64(p, v) atomicMin((unsigned long long*)(p), (unsigned long long)(v))
+#define FM_ATOMIC_ADD32(p, v) atomicAdd((int*)(p), (int)(v))
+#define FM_ATOMIC_EXCH32(p, v) atomicExch((int*)(p), (int)(v))
+#define FM_ATOMIC_MAX64(p, v) atomicMax((unsigned long long*)(p), (unsigned long long)(v))
+#else
+template <class T>
+inline T fm_host_min(T* p, T v) { T o = *p; if (v < o) *p = v; return o; }
+template <class T>
+inline T fm_host_max(T* p, T v) { T o = *p; if (v > o) *p = v; return o; }
+template <class T>
+inline T fm_host_add(T* p, T v) { T o = *p; *p = o + v; return o; }
+template <class T>
+inline T fm_host_exch(T* p, T v) { T o = *p; *p = v; return o; }
+#define FM_ATOMIC_MIN64(p, v) fm_host_min<unsigned long long>((unsigned long long*)(p), (unsigned long long)(v))
+#define FM_ATOMIC_MAX64(p, v) fm_host_max<unsigned long long>((unsigned long long*)(p), (unsigned long long)(v))
+#define FM_ATOMIC_ADD32(p, v) fm_host_add<int>((int*)(p), (int)(v))
+#define FM_ATOMIC_EXCH32(p, v) fm_host_exch<int>((int*)(p), (int)(v))
+#endif
+
+typedef unsigned long long u64;
+static const u64 kNone64 = ~0ULL;
+
+// error bits reported through DtCtx::err
+enum { FM_E_WALK = 1, FM_E_TOPOLOGY = 2, FM_E_OVERFLOW = 4 };
+
+struct DtCtx {
+  int n;                       // points
+  const double *x, *y, *z;     // internal (space-filling-curve) order
+  const int* orig;             // original 0-based id of internal point i (SoS key)
+  I4* tri;                     // vertices (x,y,z), CCW seen from outside; w unused
+  I4* adj;                     // adj[k] = (neighbour << 2 | its edge index) across the edge
+                               // opposite vertex k (the reference's adjDT(k), DV:656-669)
+  int* loc;                    // per point: slot of a triangle near/containing it, -1 = inserted
+  u64* winner;                 // per triangle: min over its points of (priority << 32 | point)
+  int* rank;                   // per triangle: exclusive scan of "splits this round"
+  int n_tri;                   // triangles alive at the start of the round
+  // flip rounds
+  int stamp;                   // global sub-round counter (>= 1)
+  u64* vote;                   // per triangle: (~stamp << 32 | voter) claimed by atomicMin
+  int* flip_edge;              // per active triangle: edge it wants to flip, -1 none
+  int* role;                   // per triangle: stamp << 2 | (1 winner, 2 partner)
+  u64* mailbox;                // per (triangle, edge): stamp << 32 | new encoded neighbour
+  int* amark;                  // per triangle: last stamp it was queued for
+  const int* active;           // triangles to check this sub-round
+  int n_active;
+  int* next_active;            // queue for the next sub-round
+  int* counters;               // [0] next_active length, [1] splits, [2] flips, [3] walk steps
+  int* err;
+};
+
+FM_HD inline P3 ldp(const DtCtx& c, int i) { return P3{c.x[i], c.y[i], c.z[i]}; }
+FM_HD inline int enc(int t, int e) { return (t << 2) | e; }
+FM_HD inline int geti(const I4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+FM_HD inline void seti(I4& v, int k, int val) {
+  if (k == 0) v.x = val; else if (k == 1) v.y = val; else v.z = val;
+}
+FM_HD inline unsigned hash32(unsigned v) {  // bijective mixer: insertion priority
+  v ^= v >> 16; v *= 0x7feb352dU; v ^= v >> 15; v *= 0x846ca68bU; v ^= v >> 16;
+  return v;
+}
+
+// 63-bit Morton key of a point of the unit sphere (21 bits per axis): the
+// internal point order, so that neighbouring generators are neighbours in HBM.
+FM_HD inline u64 spread21(u64 v) {
+  v &= 0x1fffffULL;
+  v = (v | v << 32) & 0x1f00000000ffffULL;
+  v = (v | v << 16) & 0x1f0000ff0000ffULL;
+  v = (v | v << 8) & 0x100f00f00f00f00fULL;
+  v = (v | v << 4) & 0x10c30c30c30c30c3ULL;
+  v = (v | v << 2) & 0x1249249249249249ULL;
+  return v;
+}
+FM_HD inline u64 morton_key(double x, double y, double z) {
+  const double s = 1048575.5;  // maps [-1,1] onto [0, 2^21)
+  double fx = fmin(fmax((x + 1.0) * s, 0.0), 2097151.0);
+  double fy = fmin(fmax((y + 1.0) * s, 0.0), 2097151.0);
+  double fz = fmin(fmax((z + 1.0) * s, 0.0), 2097151.0);
+  return spread21((u64)fx) | (spread21((u64)fy) << 1) | (spread21((u64)fz) << 2);
+}
+
+FM_HD inline void queue_active(const DtCtx& c, int t, int stamp) {
+  if (FM_ATOMIC_EXCH32(&c.amark[t], stamp) != stamp) {
+    int pos = FM_ATOMIC_ADD32(&c.counters[0], 1);
+    c.next_active[pos] = t;
+  }
+}
+
+// ------------------------------------------------------------ point location
+// One thread per point.  Replaces the bucket bookkeeping of DV:247-293 and
+// DV:303-317: a visibility walk from the remembered slot to the triangle that
+// contains the point (three orient tests per step, the edge just crossed is
+// not re-tested), then a vote for that triangle.
+struct KLocateVote {
+  FM_HD static void run(const DtCtx& c, int p) {
+    int t = c.loc[p];
+    if (t < 0) return;
+    P3 q = ldp(c, p);
+    int qi = c.orig[p];
+    int from = -1, steps = 0;
+    for (;;) {
+      I4 v = c.tri[t];
+      I4 a = c.adj[t];
+      P3 pa = ldp(c, v.x), pb = ldp(c, v.y), pc = ldp(c, v.z);
+      int ia = c.orig[v.x], ib = c.orig[v.y], ic = c.orig[v.z];
+      int next = -1;
+      // edge opposite vertex k is (v[k+1], v[k+2]); q must be on its left
+      if ((a.x >> 2) != from && orient(pb, pc, q, ib, ic, qi) < 0) next = a.x >> 2;
+      else if ((a.y >> 2) != from && orient(pc, pa, q, ic, ia, qi) < 0) next = a.y >> 2;
+      else if ((a.z >> 2) != from && orient(pa, pb, q, ia, ib, qi) < 0) next = a.z >> 2;
+      if (next < 0) break;
+      from = t;
+      t = next;
+      if (++steps > (1 << 20)) { *c.err |= FM_E_WALK; return; }
+    }
+    c.loc[p] = t;
+    u64 key = ((u64)hash32((unsigned)qi) << 32) | (unsigned)p;
+    FM_ATOMIC_MIN64(&c.winner[t], key);
+  }
+};
+
+// One thread per triangle: 1 if it splits this round (input of the scan).
+struct KSplitFlag {
+  FM_HD static void run(const DtCtx& c, int t) { c.rank[t] = (c.winner[t] != kNone64) ? 1 : 0; }
+};
+
+// ------------------------------------------------------------------ 1->3 split
+// One thread per triangle that won a point p.  (a,b,c) becomes
+//   A = (a,b,p) in slot t,  B = (b,c,p) in slot s1,  C = (c,a,p) in slot s1+1,
+// the new vertex always last (as DV:977-982), so the edge inherited from the
+// parent is edge 2 of each child.  A neighbour that splits in the same launch is
+// not touched: where ITS child will be follows from its winner and rank alone.
+struct KSplit {
+  FM_HD static int child_slot(const DtCtx& c, int n, int e) {
+    // slot of the child of (splitting) triangle n that inherits n's edge e
+    int s1 = c.n_tri + 2 * c.rank[n];
+    return e == 2 ? n : (e == 0 ? s1 : s1 + 1);
+  }
+  FM_HD static void run(const DtCtx& c, int t) {
+    u64 w = c.winner[t];
+    if (w == kNone64) return;
+    int p = (int)(w & 0xffffffffULL);
+    I4 v = c.tri[t];
+    I4 a = c.adj[t];
+    int s1 = c.n_tri + 2 * c.rank[t], s2 = s1 + 1;
+    int childOf[3] = {s1, s2, t};  // parent edge k -> child slot
+    int outer[3];
+    for (int k = 0; k < 3; k++) {
+      int ne = geti(a, k), n = ne >> 2, e = ne & 3;
+      if (c.winner[n] != kNone64) {
+        outer[k] = enc(child_slot(c, n, e), 2);
+      } else {
+        outer[k] = ne;
+        ((int*)&c.adj[n])[e] = enc(childOf[k], 2);
+      }
+    }
+    c.tri[t] = I4{v.x, v.y, p, 0};
+    c.adj[t] = I4{enc(s1, 1), enc(s2, 0), outer[2], 0};
+    c.tri[s1] = I4{v.y, v.z, p, 0};
+    c.adj[s1] = I4{enc(s2, 1), enc(t, 0), outer[0], 0};
+    c.tri[s2] = I4{v.z, v.x, p, 0};
+    c.adj[s2] = I4{enc(t, 1), enc(s1, 0), outer[1], 0};
+    c.loc[p] = -1;
+    queue_active(c, t, c.stamp);
+    queue_active(c, s1, c.stamp);
+    queue_active(c, s2, c.stamp);
+    FM_ATOMIC_ADD32(&c.counters[1], 1);
+  }
+};
+
+// ---------------------------------------------------------------- flip rounds
+// Sub-round = check -> mark -> flip -> patch.  validate_DT (DV:845-882) tests the
+// vertex opposite the new point's triangle with in_circle and flips on INSIDE;
+// here every queued triangle tests its three edges and asks for the first
+// violated one.  A flip needs both triangles: the pair belongs to the lowest
+// voter (atomicMin), the others retry in the next sub-round.
+FM_HD inline u64 vote_key(int stamp, int t) {
+  return ((u64)(0x7fffffffu - (unsigned)stamp) << 32) | (unsigned)t;
+}
+
+struct KCheck {
+  FM_HD static void run(const DtCtx& c, int i) {
+    int t = c.active[i];
+    I4 v = c.tri[t];
+    I4 a = c.adj[t];
+    P3 pa = ldp(c, v.x), pb = ldp(c, v.y), pc = ldp(c, v.z);
+    int ia = c.orig[v.x], ib = c.orig[v.y], ic = c.orig[v.z];
+    int fe = -1;
+    for (int k = 0; k < 3; k++) {
+      int ne = geti(a, k), n = ne >> 2, e = ne & 3;
+      int d = geti(c.tri[n], e);
+      if (incircle(pa, pb, pc, ldp(c, d), ia, ib, ic, c.orig[d]) > 0) { fe = k; break; }
+    }
+    c.flip_edge[t] = fe;
+    if (fe >= 0) {
+      u64 key = vote_key(c.stamp, t);
+      FM_ATOMIC_MIN64(&c.vote[t], key);
+      FM_ATOMIC_MIN64(&c.vote[geti(a, fe) >> 2], key);
+    }
+  }
+};
+
+struct KMark {
+  FM_HD static void run(const DtCtx& c, int i) {
+    int t = c.active[i];
+    int fe = c.flip_edge[t];
+    if (fe < 0) return;
+    int n = geti(c.adj[t], fe) >> 2;
+    u64 key = vote_key(c.stamp, t);
+    if (c.vote[t] == key && c.vote[n] == key) {
+      c.role[t] = (c.stamp << 2) | 1;
+      c.role[n] = (c.stamp << 2) | 2;
+    } else {
+      queue_active(c, t, c.stamp + 1);  // lost the vote: try again next sub-round
+    }
+  }
+};
+
+// Flip of the edge opposite vertex k of t = (a,b,c) (rotated so that a = v[k]),
+// shared with n whose opposite vertex is d:
+//   X = (a,b,d) -> slot t      Y = (a,d,c) -> slot n           (flip22, DV:1098-1149)
+// Outer edges move:  (t, c's index) -> (t,2)   (t, b's index) -> (n,1)
+//                    (n, c's index) -> (t,0)   (n, b's index) -> (n,0)
+struct FlipGeom {
+  int t, n, k, e;
+  int so[4], io[4];  // old (slot, edge) of the four outer edges
+  int sn[4], in[4];  // new (slot, edge)
+};
+FM_HD inline FlipGeom flip_geom(int t, int k, int n, int e) {
+  FlipGeom g;
+  g.t = t; g.n = n; g.k = k; g.e = e;
+  int kb = (k + 1) % 3, kc = (k + 2) % 3;  // b, c in t
+  int ec = (e + 1) % 3, eb = (e + 2) % 3;  // n = (d, c, b) from e
+  g.so[0] = t; g.io[0] = kc; g.sn[0] = t; g.in[0] = 2;
+  g.so[1] = t; g.io[1] = kb; g.sn[1] = n; g.in[1] = 1;
+  g.so[2] = n; g.io[2] = ec; g.sn[2] = t; g.in[2] = 0;
+  g.so[3] = n; g.io[3] = eb; g.sn[3] = n; g.in[3] = 0;
+  return g;
+}
+
+struct KFlip {
+  FM_HD static void run(const DtCtx& c, int i) {
+    int t = c.active[i];
+    if (c.role[t] != ((c.stamp << 2) | 1)) return;
+    int k = c.flip_edge[t];
+    I4 vt = c.tri[t], at = c.adj[t];
+    int ne = geti(at, k), n = ne >> 2, e = ne & 3;
+    I4 vn = c.tri[n], an = c.adj[n];
+    FlipGeom g = flip_geom(t, k, n, e);
+    int va = geti(vt, k), vb = geti(vt, (k + 1) % 3), vc = geti(vt, (k + 2) % 3), vd = geti(vn, e);
+    int outer[4];
+    for (int j = 0; j < 4; j++) {
+      int oe = geti(g.so[j] == t ? at : an, g.io[j]);
+      int m = oe >> 2, em = oe & 3;
+      outer[j] = oe;
+      int nw = enc(g.sn[j], g.in[j]);
+      if ((c.role[m] >> 2) == c.stamp) {
+        c.mailbox[3 * (size_t)m + em] = ((u64)(unsigned)c.stamp << 32) | (unsigned)nw;
+      } else {
+        ((int*)&c.adj[m])[em] = nw;
+      }
+    }
+    c.tri[t] = I4{va, vb, vd, e};  // w keeps e for KPatch
+    c.adj[t] = I4{outer[2], enc(n, 2), outer[0], 0};
+    c.tri[n] = I4{va, vd, vc, 0};
+    c.adj[n] = I4{outer[3], outer[1], enc(t, 1), 0};
+    queue_active(c, t, c.stamp + 1);
+    queue_active(c, n, c.stamp + 1);
+    FM_ATOMIC_ADD32(&c.counters[2], 1);
+  }
+};
+
+// After all flips of the sub-round: a pair whose outer neighbour flipped too
+// finds that neighbour's new (slot, edge) in the mailbox of its OLD (slot, edge).
+// The pre-flip indices come back from flip_edge[t] (k) and tri[t].w (e).
+struct KPatch {
+  FM_HD static void run(const DtCtx& c, int i) {
+    int t = c.active[i];
+    if (c.role[t] != ((c.stamp << 2) | 1)) return;
+    int k = c.flip_edge[t];
+    int n = c.adj[t].y >> 2;
+    int e = c.tri[t].w;
+    FlipGeom g = flip_geom(t, k, n, e);
+    for (int j = 0; j < 4; j++) {
+      u64 msg = c.mailbox[3 * (size_t)g.so[j] + g.io[j]];
+      if ((int)(msg >> 32) == c.stamp) ((int*)&c.adj[g.sn[j]])[g.in[j]] = (int)(msg & 0xffffffffULL);
+    }
+  }
+};
+
+}  // namespace fm
