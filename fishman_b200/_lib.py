@@ -1,0 +1,63 @@
+"""ctypes binding of the C ABI (include/fishman_b200.h).  The library is the
+product: there is no Python or CPU implementation behind it, and loading or
+using it without a CUDA device raises."""
+import ctypes as C
+import os
+
+from . import build as _build
+
+_lib = None
+
+SYMBOLS = [
+    "fm_create", "fm_create_lonlat", "fm_create_dist", "fm_destroy", "fm_last_error", "fm_triangulate",
+    "fm_counts", "fm_get_triangles", "fm_voronoi", "fm_get_circumcentres", "fm_get_rings",
+    "fm_get_edges", "fm_lloyd", "fm_lloyd_local", "fm_generator_block", "fm_get_generators",
+    "fm_set_generators", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
+    "fm_profile_enable", "fm_profile_get", "fm_device_info",
+]
+
+
+class Density(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("cx", C.c_double), ("cy", C.c_double), ("cz", C.c_double),
+                ("beta", C.c_double), ("alpha", C.c_double), ("gamma", C.c_double)]
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} is missing: run `python -m fishman_b200.build` (needs nvcc); "
+                           "fishman_b200 has no CPU fallback")
+    L = C.CDLL(path)
+    vp, dp, ip = C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int32)
+    i32, i64p = C.c_int32, C.POINTER(C.c_int64)
+    L.fm_create.argtypes = [i32, dp, dp, dp, C.POINTER(vp)]
+    L.fm_create_lonlat.argtypes = [i32, dp, dp, C.POINTER(vp)]
+    L.fm_create_dist.argtypes = [i32, dp, dp, dp, i32, i32, C.POINTER(vp)]
+    L.fm_destroy.argtypes = [vp]
+    L.fm_destroy.restype = None
+    L.fm_last_error.argtypes = [vp]
+    L.fm_last_error.restype = C.c_char_p
+    L.fm_triangulate.argtypes = [vp]
+    L.fm_counts.argtypes = [vp, ip, ip]
+    L.fm_get_triangles.argtypes = [vp, ip, ip]
+    L.fm_voronoi.argtypes = [vp, i32]
+    L.fm_get_circumcentres.argtypes = [vp, dp, dp]
+    L.fm_get_rings.argtypes = [vp, ip, ip, ip]
+    L.fm_get_edges.argtypes = [vp, ip, ip, ip]
+    L.fm_lloyd.argtypes = [vp, C.POINTER(Density), i32, C.c_double, i32, ip, dp]
+    L.fm_lloyd_local.argtypes = [vp, C.POINTER(Density), i32, dp]
+    L.fm_generator_block.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), i64p, i64p, i64p]
+    L.fm_get_generators.argtypes = [vp, dp, dp, dp]
+    L.fm_set_generators.argtypes = [vp, dp, dp, dp]
+    L.fm_timer_begin.argtypes = [vp]
+    L.fm_timer_end.argtypes = [vp, dp]
+    L.fm_stats.argtypes = [vp, i64p]
+    L.fm_stats_reset.argtypes = [vp]
+    L.fm_profile_enable.argtypes = [vp, i32]
+    L.fm_profile_get.argtypes = [vp, i32, C.c_void_p, i64p, dp, i64p, ip]
+    L.fm_device_info.argtypes = [C.c_char_p, i32, ip]
+    _lib = L
+    return L

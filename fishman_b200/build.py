@@ -1,0 +1,32 @@
+"""Builds fishman_b200/libfishman_b200.so (nvcc, sm_100a only) in-tree."""
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "libfishman_b200.so")
+SRC = os.path.join(HERE, "csrc", "fishman_b200.cu")
+DEPS = [os.path.join(HERE, "csrc", f) for f in
+        ("fishman_b200.cu", "predicates.cuh", "sos_tables.inc", "dt_kernels.cuh", "dt_driver.h",
+         "vd_kernels.cuh")] + [os.path.join(HERE, "..", "include", "fishman_b200.h")]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+
+def stale():
+    if not os.path.exists(LIB):
+        return True
+    t = os.path.getmtime(LIB)
+    return any(os.path.getmtime(d) > t for d in DEPS)
+
+
+def build(force=False, verbose=False):
+    if not (force or stale()):
+        return LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, SRC]
+    subprocess.check_call(cmd)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force=True, verbose=True))

@@ -130,14 +130,45 @@ int dt_bootstrap(B& be, DtCtx& c, int boot[4], char* msg, size_t msglen) {
   return 0;
 }
 
+// Flip sub-rounds until the queue runs dry.  cur holds nact queued triangles
+// (queued with stamp *stamp).  Returns 0 or 1 (msg filled).
+template <class B>
+int dt_flip_loop(B& be, DtCtx& c, int* cur, int* nxt, int nact, int* stamp, DtStats* st, char* msg,
+                 size_t msglen) {
+  int zero[4] = {0, 0, 0, 0}, host[4];
+  while (nact > 0) {
+    st->subrounds++;
+    if (nact > st->max_active) st->max_active = nact;
+    be.write_ints(c.counters, zero, 1);
+    c.stamp = *stamp;
+    c.active = cur;
+    c.n_active = nact;
+    c.next_active = nxt;
+    be.template launch<KCheck>(c, nact);
+    be.template launch<KMark>(c, nact);
+    be.template launch<KFlip>(c, nact);
+    be.template launch<KPatch>(c, nact);
+    be.read_ints(host, c.counters, 4);
+    nact = host[0];
+    st->flips = host[2];
+    (*stamp)++;
+    int* tmp = cur; cur = nxt; nxt = tmp;
+    if (*stamp > (1 << 28)) {
+      snprintf(msg, msglen, "flip rounds did not terminate");
+      return 1;
+    }
+  }
+  return 0;
+}
+
 // Runs insertion rounds until every point is a vertex.  Preconditions: the four
 // bootstrap faces are in slots 0..3, loc[] is 0 for every point but the
-// bootstrap ones (-1), vote[] is all ones, role/amark/mailbox are zero.
-// listA/listB: two int queues of max_tri entries.
+// bootstrap ones (-1), vote[] is all ones, role/amark/mailbox hold stamps older
+// than *stamp (zero at first use).  listA/listB: two int queues of 2n-4 entries.
 template <class B>
-int dt_run(B& be, DtCtx& c, int* listA, int* listB, DtStats* st, char* msg, size_t msglen) {
+int dt_run(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, char* msg,
+           size_t msglen) {
   int remaining = c.n - 4;
-  int stamp = 1;
   c.n_tri = 4;
   memset(st, 0, sizeof *st);
   int zero[4] = {0, 0, 0, 0}, host[4];
@@ -158,38 +189,32 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, DtStats* st, char* msg, size
       return 1;
     }
     be.write_ints(c.counters, zero, 1);
-    c.stamp = stamp;
+    c.stamp = *stamp;
     c.next_active = listA;
     be.template launch<KSplit>(c, c.n_tri);
     remaining -= nsplit;
     c.n_tri += 2 * nsplit;
-    int nact = 3 * nsplit;
-    int* cur = listA;
-    int* nxt = listB;
-    while (nact > 0) {
-      st->subrounds++;
-      if (nact > st->max_active) st->max_active = nact;
-      be.write_ints(c.counters, zero, 1);
-      c.stamp = stamp;
-      c.active = cur;
-      c.n_active = nact;
-      c.next_active = nxt;
-      be.template launch<KCheck>(c, nact);
-      be.template launch<KMark>(c, nact);
-      be.template launch<KFlip>(c, nact);
-      be.template launch<KPatch>(c, nact);
-      be.read_ints(host, c.counters, 4);
-      nact = host[0];
-      st->flips = host[2];
-      stamp++;
-      int* tmp = cur; cur = nxt; nxt = tmp;
-      if (stamp > (1 << 28)) {
-        snprintf(msg, msglen, "flip rounds did not terminate");
-        return 1;
-      }
-    }
+    if (dt_flip_loop(be, c, listA, listB, 3 * nsplit, stamp, st, msg, msglen)) return 1;
   }
   return 0;
+}
+
+// Warm restart: the connectivity of the previous triangulation with moved
+// vertices.  Returns 0 repaired, 2 when a triangle turned over (caller rebuilds
+// from scratch), 1 on error.
+template <class B>
+int dt_repair(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, char* msg,
+              size_t msglen) {
+  int zero[4] = {0, 0, 0, 0}, host[4];
+  memset(st, 0, sizeof *st);
+  be.write_ints(c.counters, zero, 4);
+  c.stamp = *stamp;
+  c.next_active = listA;
+  be.template launch<KValidate>(c, c.n_tri);
+  be.template launch<KQueueAll>(c, c.n_tri);
+  be.read_ints(host, c.counters, 4);
+  if (host[3] > 0) return 2;
+  return dt_flip_loop(be, c, listA, listB, c.n_tri, stamp, st, msg, msglen);
 }
 
 }  // namespace fm

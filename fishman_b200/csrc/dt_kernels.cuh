@@ -316,4 +316,23 @@ struct KPatch {
   }
 };
 
+// ------------------------------------------------------------- warm restart
+// After the generators moved (Lloyd), the old connectivity is still a valid
+// triangulation as long as no triangle turned over; it is then repaired by flip
+// rounds alone instead of being rebuilt.  KValidate counts triangles that are
+// not strictly CCW any more (counters[3]); KQueueAll queues every triangle.
+struct KValidate {
+  FM_HD static void run(const DtCtx& c, int t) {
+    I4 v = c.tri[t];
+    if (orient(ldp(c, v.x), ldp(c, v.y), ldp(c, v.z), c.orig[v.x], c.orig[v.y], c.orig[v.z]) <= 0)
+      FM_ATOMIC_ADD32(&c.counters[3], 1);
+  }
+};
+struct KQueueAll {
+  FM_HD static void run(const DtCtx& c, int t) {
+    c.next_active[t] = t;
+    c.amark[t] = c.stamp;
+  }
+};
+
 }  // namespace fm

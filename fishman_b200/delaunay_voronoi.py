@@ -1,0 +1,236 @@
+"""Host-side mirror of the reference's delaunay_voronoi_mod interface
+(/root/reference/src/delaunay_voronoi_mod.F90:15-30) over the C ABI.
+
+The reference module keeps its mesh in module-level state and exposes four
+procedures, called in this order by gen_mesh (/root/reference/src/gen_mesh.F90:25-28):
+
+    delaunay_voronoi_init(num_point, lon=, lat= | x=, y=, z=)     DV:188
+    delaunay_triangulation()                                      DV:226
+    voronoi_diagram(all=)                                         DV:358
+    delaunay_voronoi_output(output)                               DV:587
+
+`Mesh` carries the same four steps as methods (one handle per mesh instead of
+global state, which is what makes a Lloyd loop possible at all -- SURVEY.md F5);
+the module-level functions of the same names keep one default mesh, like the
+Fortran.  All ids are 1-based as in the reference.  Errors raise FishmanError
+(the reference calls log_error -> stop 1).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import Density
+
+
+class FishmanError(RuntimeError):
+    pass
+
+
+def density_uniform():
+    return Density(0, 0.0, 0.0, 1.0, 0.0, 1.0, 1.0)
+
+
+def density_x4(lon_deg=0.0, lat_deg=40.0, beta=np.pi / 6, alpha=np.pi / 20, gamma=0.25 ** 4):
+    """4:1 regional refinement of SURVEY.md 7.3 (spacing ~ rho**-1/4)."""
+    lon, lat = np.deg2rad(lon_deg), np.deg2rad(lat_deg)
+    return Density(1, float(np.cos(lat) * np.cos(lon)), float(np.cos(lat) * np.sin(lon)),
+                   float(np.sin(lat)), float(beta), float(alpha), float(gamma))
+
+
+def _d(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _i(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int32))
+
+
+class Mesh:
+    def __init__(self, num_point=None, lon=None, lat=None, x=None, y=None, z=None, rank=0, size=1):
+        """delaunay_voronoi_init: either lon/lat or x/y/z (DV:204-220)."""
+        L = _lib.lib()
+        self._h = C.c_void_p()
+        if x is not None:
+            cols = [np.ascontiguousarray(v, dtype=np.float64) for v in (x, y, z)]
+            n = len(cols[0]) if num_point is None else int(num_point)
+            if size == 1:
+                rc = L.fm_create(n, _d(cols[0]), _d(cols[1]), _d(cols[2]), C.byref(self._h))
+            else:
+                rc = L.fm_create_dist(n, _d(cols[0]), _d(cols[1]), _d(cols[2]), rank, size, C.byref(self._h))
+        elif lon is not None:
+            cols = [np.ascontiguousarray(v, dtype=np.float64) for v in (lon, lat)]
+            n = len(cols[0]) if num_point is None else int(num_point)
+            rc = L.fm_create_lonlat(n, _d(cols[0]), _d(cols[1]), C.byref(self._h))
+        else:
+            raise FishmanError("delaunay_voronoi_init needs lon/lat or x/y/z")
+        if rc:
+            raise FishmanError(L.fm_last_error(None).decode())
+        self.n = n
+        self.n_tri = 2 * n - 4
+        self.n_edge = 3 * n - 6
+        self.rank, self.size = rank, size
+
+    @classmethod
+    def from_xyz(cls, xyz, **kw):
+        xyz = np.asarray(xyz, dtype=np.float64)
+        return cls(x=xyz[:, 0], y=xyz[:, 1], z=xyz[:, 2], **kw)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.lib().fm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc):
+        if rc:
+            raise FishmanError(_lib.lib().fm_last_error(self._h).decode())
+
+    # ---- the reference's call sequence
+    def delaunay_triangulation(self):
+        self._chk(_lib.lib().fm_triangulate(self._h))
+
+    def voronoi_diagram(self, all=False):
+        self._chk(_lib.lib().fm_voronoi(self._h, 1 if all else 0))
+
+    def delaunay_voronoi_output(self, output, tag=None):
+        """Calls output(DVT, DT, DE, VVT, VC, VE, tag) with flat arrays in the
+        roles of the reference's six containers (output_interface, DV:169-181)."""
+        tri, adj = self.triangles()
+        xyz, lonlat = self.circumcentres()
+        off, rt, rn = self.rings()
+        g = self.generators()
+        try:
+            de, ve_vvt, ve_vc = self.edges()
+        except FishmanError:
+            de = ve_vvt = ve_vc = None
+        return output(dict(xyz=g), dict(tri=tri, adj=adj), dict(dvt=de), dict(xyz=xyz, lonlat=lonlat),
+                      dict(off=off, vvt=rt, adj=rn), dict(vvt=ve_vvt, vc=ve_vc), tag)
+
+    # ---- accessors (get_DT / get_VVT / get_VC / get_DE / get_VE)
+    def triangles(self):
+        tri = np.empty((self.n_tri, 3), dtype=np.int32)
+        adj = np.empty((self.n_tri, 3), dtype=np.int32)
+        self._chk(_lib.lib().fm_get_triangles(self._h, _i(tri), _i(adj)))
+        return tri, adj
+
+    def circumcentres(self):
+        xyz = np.empty((self.n_tri, 3))
+        lonlat = np.empty((self.n_tri, 2))
+        self._chk(_lib.lib().fm_get_circumcentres(self._h, _d(xyz), _d(lonlat)))
+        return xyz, lonlat
+
+    def rings(self):
+        off = np.empty(self.n + 1, dtype=np.int32)
+        rt = np.empty(3 * self.n_tri, dtype=np.int32)
+        rn = np.empty(3 * self.n_tri, dtype=np.int32)
+        self._chk(_lib.lib().fm_get_rings(self._h, _i(off), _i(rt), _i(rn)))
+        return off, rt, rn
+
+    def edges(self):
+        de = np.empty((self.n_edge, 2), dtype=np.int32)
+        vv = np.empty((self.n_edge, 2), dtype=np.int32)
+        vc = np.empty((self.n_edge, 2), dtype=np.int32)
+        self._chk(_lib.lib().fm_get_edges(self._h, _i(de), _i(vv), _i(vc)))
+        return de, vv, vc
+
+    def generators(self):
+        g = np.empty((3, self.n))
+        self._chk(_lib.lib().fm_get_generators(self._h, _d(g[0]), _d(g[1]), _d(g[2])))
+        return np.ascontiguousarray(g.T)
+
+    def set_generators(self, xyz):
+        g = np.ascontiguousarray(np.asarray(xyz, dtype=np.float64).T)
+        self._chk(_lib.lib().fm_set_generators(self._h, _d(g[0]), _d(g[1]), _d(g[2])))
+
+    # ---- Lloyd
+    def lloyd(self, rho=None, max_iter=1, tol=0.0, warm=True):
+        rho = rho or density_uniform()
+        it = C.c_int32(0)
+        md = C.c_double(0.0)
+        self._chk(_lib.lib().fm_lloyd(self._h, C.byref(rho), int(max_iter), float(tol), 1 if warm else 0,
+                                      C.byref(it), C.byref(md)))
+        return it.value, md.value
+
+    def lloyd_local(self, rho=None, warm=True):
+        rho = rho or density_uniform()
+        md = C.c_double(0.0)
+        self._chk(_lib.lib().fm_lloyd_local(self._h, C.byref(rho), 1 if warm else 0, C.byref(md)))
+        return md.value
+
+    def generator_block(self):
+        """Device pointers and block bounds for the generator all-gather."""
+        px, py, pz = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        npad, beg, cnt = C.c_int64(), C.c_int64(), C.c_int64()
+        self._chk(_lib.lib().fm_generator_block(self._h, C.byref(px), C.byref(py), C.byref(pz),
+                                                C.byref(npad), C.byref(beg), C.byref(cnt)))
+        return (px.value, py.value, pz.value), npad.value, beg.value, cnt.value
+
+    # ---- measurement
+    def timer_begin(self):
+        self._chk(_lib.lib().fm_timer_begin(self._h))
+
+    def timer_end(self):
+        ms = C.c_double(0.0)
+        self._chk(_lib.lib().fm_timer_end(self._h, C.byref(ms)))
+        return ms.value
+
+    def stats(self):
+        s = np.zeros(8, dtype=np.int64)
+        _lib.lib().fm_stats(self._h, s.ctypes.data_as(C.POINTER(C.c_int64)))
+        keys = ("rounds", "subrounds", "flips", "max_active", "launches", "cold", "warm", "_")
+        return dict(zip(keys, (int(v) for v in s)))
+
+    def stats_reset(self):
+        _lib.lib().fm_stats_reset(self._h)
+
+    def profile(self, on):
+        _lib.lib().fm_profile_enable(self._h, 1 if on else 0)
+
+    def profile_rows(self):
+        cap = 64
+        names = (C.c_char * 32 * cap)()
+        la = np.zeros(cap, dtype=np.int64)
+        th = np.zeros(cap, dtype=np.int64)
+        ms = np.zeros(cap)
+        rows = C.c_int32(0)
+        _lib.lib().fm_profile_get(self._h, cap, C.cast(names, C.c_void_p),
+                                  la.ctypes.data_as(C.POINTER(C.c_int64)), _d(ms),
+                                  th.ctypes.data_as(C.POINTER(C.c_int64)), C.byref(rows))
+        return [dict(name=names[k].value.decode(), launches=int(la[k]), ms=float(ms[k]), threads=int(th[k]))
+                for k in range(rows.value)]
+
+
+# ---- module-level mirror with one default mesh, like the Fortran module state
+_default = None
+
+
+def delaunay_voronoi_init(num_point=None, lon=None, lat=None, x=None, y=None, z=None):
+    global _default
+    if _default is not None:
+        _default.close()
+    _default = Mesh(num_point, lon=lon, lat=lat, x=x, y=y, z=z)
+    return _default
+
+
+def delaunay_triangulation():
+    _default.delaunay_triangulation()
+
+
+def voronoi_diagram(all=False):
+    _default.voronoi_diagram(all=all)
+
+
+def delaunay_voronoi_output(output, tag=None):
+    return _default.delaunay_voronoi_output(output, tag)
+
+
+def canonical_triangles(tri):
+    """Lexicographically sorted rows of sorted vertex triples."""
+    t = np.sort(np.asarray(tri, dtype=np.int64), axis=1)
+    return t[np.lexsort((t[:, 2], t[:, 1], t[:, 0]))]

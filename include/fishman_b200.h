@@ -1,0 +1,119 @@
+/*
+ * fishman_b200.h -- C ABI of the B200 (sm_100a) implementation of fishman's SCVT
+ * inner loop: spherical Delaunay triangulation, dual Voronoi diagram and the
+ * Lloyd centroid update.
+ *
+ * This is the boundary a Fortran host binds with ISO_C_BINDING (the stub is in
+ * fishman_b200/fortran/fishman_gpu_c.F90 and INTEGRATION.md).  Each entry point
+ * names the reference procedure it replaces; "DV" is
+ * /root/reference/src/delaunay_voronoi_mod.F90, "SG" is
+ * /root/reference/src/sphere_geometry_mod.F90, "MM" is
+ * /root/reference/src/mpas_mesh_mod.F90.
+ *
+ * Conventions (those of the reference):
+ *   - every id that crosses the boundary is 1-based; cell / generator ids are the
+ *     input order (DV:341-344);
+ *   - triangles are counter-clockwise seen from outside the sphere (DV:1882-1885);
+ *   - adj[k] is the triangle across the edge opposite vertex k (DV:656-669);
+ *   - ring_nbr[j] lies on the edge shared by ring_tri[j] and ring_tri[j+1]
+ *     (DV:723-738); rings start at their smallest neighbour id;
+ *   - lon is in [0, 2 pi) (SG:119);
+ *   - T = 2N-4 triangles, E = 3N-6 edges (euler_formula, SG:57-71).
+ * Every function returns 0 on success; on failure it returns non-zero and
+ * fm_last_error() describes it (the Fortran shim turns that into log_error ->
+ * stop 1, the reference's only error convention, lib/flogger/src/log_mod.F90:99).
+ * There is no CPU fallback: without a CUDA device fm_create fails.
+ * A handle is not thread-safe; distinct handles are independent.
+ */
+#ifndef FISHMAN_B200_H
+#define FISHMAN_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fm_handle fm_handle;
+
+/* Density function of the Lloyd step (the reference has none).
+ * kind 0: rho = 1.  kind 1: rho(x) = (1-gamma)/2 (tanh((beta - d(x,c))/alpha) + 1) + gamma,
+ * d = great-circle distance to the unit vector c (calc_arc_length, SG:289-296). */
+typedef struct fm_density {
+  int32_t kind;
+  double cx, cy, cz, beta, alpha, gamma;
+} fm_density;
+
+/* delaunay_voronoi_init(num_point, x=, y=, z=)  DV:188-224.  Copies the n generators to
+ * the device (contiguous arrays: the shim packs strided sections first), orders them
+ * along a space-filling curve internally and rejects duplicate points (DV:286-288). */
+int fm_create(int32_t n, const double* x, const double* y, const double* z, fm_handle** out);
+/* delaunay_voronoi_init(num_point, lon=, lat=)  DV:204-211 (cartesian_transform, SG:87-98) */
+int fm_create_lonlat(int32_t n, const double* lon, const double* lat, fm_handle** out);
+/* Sharded variant: this process is rank `rank` of `size`; the Lloyd centroid stage then
+ * updates only the rank's contiguous block of the internal (space-filling-curve)
+ * order, see fm_lloyd_local / fm_generator_block. */
+int fm_create_dist(int32_t n, const double* x, const double* y, const double* z, int32_t rank,
+                   int32_t size, fm_handle** out);
+void fm_destroy(fm_handle* h);
+const char* fm_last_error(const fm_handle* h); /* h may be NULL: error of the last failed fm_create */
+
+/* delaunay_triangulation()  DV:226-356 */
+int fm_triangulate(fm_handle* h);
+/* sizes for the caller's buffers: T = 2N-4, E = 3N-6 (DV:413, DV:435) */
+int fm_counts(const fm_handle* h, int32_t* n_tri, int32_t* n_edge);
+/* get_DT: tri and adj are 3 x T column-major (Fortran tri(3,T)) */
+int fm_get_triangles(fm_handle* h, int32_t* tri, int32_t* adj);
+
+/* voronoi_diagram(all)  DV:358-585: circumcentres (DV:379-391), cell rings (DV:394-409) and,
+ * with all != 0, the Delaunay / Voronoi edge tables (DV:411-460). */
+int fm_voronoi(fm_handle* h, int32_t all);
+/* get_VVT: xyz 3 x T, lonlat 2 x T (either may be NULL) */
+int fm_get_circumcentres(fm_handle* h, double* xyz, double* lonlat);
+/* VC%VVT / VC%adjVC rings as CSR: off has N+1 entries (0-based offsets), ring_tri and
+ * ring_nbr have 6N-12 entries */
+int fm_get_rings(fm_handle* h, int32_t* off, int32_t* ring_tri, int32_t* ring_nbr);
+/* get_DE / get_VE (needs fm_voronoi(h, 1)): de 2 x E (DVT1 < DVT2, DV:415-432), ve_vvt 2 x E
+ * (the two Voronoi vertices = triangle ids), ve_vc 2 x E (the two cells); edge k of the
+ * Voronoi diagram is the dual of Delaunay edge k (DV:435-460). */
+int fm_get_edges(fm_handle* h, int32_t* de, int32_t* ve_vvt, int32_t* ve_vc);
+
+/* Lloyd loop (no reference code).  Runs at most max_iter iterations of
+ * triangulate -> circumcentres -> centroids -> generator update, stopping early when the
+ * largest chord displacement is <= tol.  warm != 0 repairs the previous triangulation by
+ * flip rounds when no triangle turned over, instead of rebuilding it. */
+int fm_lloyd(fm_handle* h, const fm_density* rho, int32_t max_iter, double tol, int32_t warm,
+             int32_t* iters, double* max_disp);
+/* One iteration restricted to this rank's block of cells (fm_create_dist).  The caller
+ * then all-gathers the blocks in place (fm_generator_block gives the device pointers) and
+ * the next call sees the full set.  *max_disp is the rank-local maximum. */
+int fm_lloyd_local(fm_handle* h, const fm_density* rho, int32_t warm, double* max_disp);
+/* Device layout for the generator exchange: three arrays of n_padded doubles (x, y, z in
+ * internal order); the rank's block is [begin, begin + count). */
+int fm_generator_block(fm_handle* h, void** dx, void** dy, void** dz, int64_t* n_padded,
+                       int64_t* begin, int64_t* count);
+/* generators in input order (device -> host) */
+int fm_get_generators(fm_handle* h, double* x, double* y, double* z);
+/* replace the generators (host -> device), keeping the internal order and topology */
+int fm_set_generators(fm_handle* h, const double* x, const double* y, const double* z);
+
+/* Measurement support (bench.py): wall-clock of the device work between begin/end taken
+ * with CUDA events on the handle's stream, and per-kernel accounting. */
+int fm_timer_begin(fm_handle* h);
+int fm_timer_end(fm_handle* h, double* ms);
+/* stats[0..7]: insertion rounds, flip sub-rounds, flips, largest flip queue, kernel
+ * launches since the last fm_stats_reset, cold rebuilds, warm repairs, reserved */
+int fm_stats(const fm_handle* h, int64_t* stats);
+int fm_stats_reset(fm_handle* h);
+/* Per-kernel profile: when enabled every launch is bracketed by CUDA events (slower;
+ * never inside a headline timing).  fm_profile_get fills up to cap rows of
+ * (name, launches, total_ms, threads) and returns the row count through *rows. */
+int fm_profile_enable(fm_handle* h, int32_t on);
+int fm_profile_get(fm_handle* h, int32_t cap, char (*names)[32], int64_t* launches, double* ms,
+                   int64_t* threads, int32_t* rows);
+/* name and SM count of the device in use */
+int fm_device_info(char* name, int32_t cap, int32_t* sms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -78,7 +78,8 @@ extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_
   if (dt_bootstrap(be, c, boot, g_err, sizeof g_err)) return 1;
   for (int k = 0; k < 4; k++) loc[boot[k]] = -1;
   DtStats st;
-  if (dt_run(be, c, listA.data(), listB.data(), &st, g_err, sizeof g_err)) return 1;
+  int stamp = 1;
+  if (dt_run(be, c, listA.data(), listB.data(), &stamp, &st, g_err, sizeof g_err)) return 1;
   if (c.n_tri != T) { snprintf(g_err, sizeof g_err, "triangle count %d != 2n-4", c.n_tri); return 1; }
   for (int t = 0; t < T; t++)
     for (int k = 0; k < 3; k++) {
