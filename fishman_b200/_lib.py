@@ -9,10 +9,10 @@ from . import build as _build
 _lib = None
 
 SYMBOLS = [
-    "fm_create", "fm_create_lonlat", "fm_create_dist", "fm_destroy", "fm_last_error", "fm_triangulate",
+    "fm_create", "fm_create_lonlat", "fm_create_dist", "fm_destroy", "fm_last_error", "fm_triangulate", "fm_retriangulate",
     "fm_counts", "fm_get_triangles", "fm_voronoi", "fm_get_circumcentres", "fm_get_rings",
     "fm_get_edges", "fm_lloyd", "fm_lloyd_local", "fm_generator_block", "fm_get_generators",
-    "fm_set_generators", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
+    "fm_set_generators", "fm_host_alloc", "fm_host_free", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
     "fm_profile_enable", "fm_profile_get", "fm_device_info",
 ]
 
@@ -41,6 +41,7 @@ def lib():
     L.fm_last_error.argtypes = [vp]
     L.fm_last_error.restype = C.c_char_p
     L.fm_triangulate.argtypes = [vp]
+    L.fm_retriangulate.argtypes = [vp, i32]
     L.fm_counts.argtypes = [vp, ip, ip]
     L.fm_get_triangles.argtypes = [vp, ip, ip]
     L.fm_voronoi.argtypes = [vp, i32]
@@ -52,6 +53,8 @@ def lib():
     L.fm_generator_block.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), i64p, i64p, i64p]
     L.fm_get_generators.argtypes = [vp, dp, dp, dp]
     L.fm_set_generators.argtypes = [vp, dp, dp, dp]
+    L.fm_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+    L.fm_host_free.argtypes = [vp]
     L.fm_timer_begin.argtypes = [vp]
     L.fm_timer_end.argtypes = [vp, dp]
     L.fm_stats.argtypes = [vp, i64p]

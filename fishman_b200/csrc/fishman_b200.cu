@@ -212,6 +212,7 @@ struct fm_handle {
   double *ccx = nullptr, *ccy = nullptr, *ccz = nullptr, *cclon = nullptr, *cclat = nullptr;
   int *v2t = nullptr, *deg = nullptr, *ring_tri = nullptr, *ring_nbr = nullptr;
   int *ecount = nullptr, *de = nullptr, *ve_vvt = nullptr, *ve_vc = nullptr;
+  double* stage = nullptr;  // 3n doubles: input-order staging of fm_get/set_generators
   // accounting
   DtStats last = {};
   long long n_launch = 0, n_cold = 0, n_warm = 0, tot_rounds = 0, tot_sub = 0, tot_flips = 0;
@@ -465,7 +466,7 @@ extern "C" void fm_destroy(fm_handle* h) {
   void* ptrs[] = {h->x, h->y, h->z, h->orig, h->inv, h->tri, h->adj, h->loc, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->counters, h->err, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->ccx, h->ccy, h->ccz, h->cclon, h->cclat,
-                  h->v2t, h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc};
+                  h->v2t, h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (h->pinned) cudaFreeHost(h->pinned);
@@ -541,6 +542,11 @@ static int triangulate_warm(fm_handle* h) {
 extern "C" int fm_triangulate(fm_handle* h) {
   if (triangulate_cold(h)) return 1;
   return check_device_err(h, "fm_triangulate");
+}
+
+extern "C" int fm_retriangulate(fm_handle* h, int32_t warm) {
+  if (warm ? triangulate_warm(h) : triangulate_cold(h)) return 1;
+  return check_device_err(h, "fm_retriangulate");
 }
 
 extern "C" int fm_counts(const fm_handle* h, int32_t* n_tri, int32_t* n_edge) {
@@ -725,8 +731,8 @@ extern "C" int fm_generator_block(fm_handle* h, void** dx, void** dy, void** dz,
 
 static int xfer_generators(fm_handle* h, double* x, double* y, double* z, bool to_host) {
   int n = h->n;
-  double *ix = nullptr, *iy = nullptr, *iz = nullptr;
-  FM_CUDA(dalloc(&ix, n)); FM_CUDA(dalloc(&iy, n)); FM_CUDA(dalloc(&iz, n));
+  if (!h->stage) FM_CUDA(dalloc(&h->stage, 3 * (size_t)n));
+  double *ix = h->stage, *iy = ix + n, *iz = iy + n;
   int nb = (n + 255) / 256;
   if (to_host) {
     fm_scatter_orig<<<nb, 256, 0, h->stream>>>(n, h->orig, h->x, h->y, h->z, ix, iy, iz);
@@ -742,7 +748,6 @@ static int xfer_generators(fm_handle* h, double* x, double* y, double* z, bool t
   }
   h->n_launch++;
   FM_CUDA(cudaStreamSynchronize(h->stream));
-  cudaFree(ix); cudaFree(iy); cudaFree(iz);
   return 0;
 }
 
@@ -752,6 +757,11 @@ extern "C" int fm_get_generators(fm_handle* h, double* x, double* y, double* z) 
 extern "C" int fm_set_generators(fm_handle* h, const double* x, const double* y, const double* z) {
   return xfer_generators(h, (double*)x, (double*)y, (double*)z, false);
 }
+
+extern "C" int fm_host_alloc(size_t bytes, void** out) {
+  return cudaMallocHost(out, bytes) == cudaSuccess ? 0 : 1;
+}
+extern "C" int fm_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? 0 : 1; }
 
 extern "C" int fm_timer_begin(fm_handle* h) {
   FM_CUDA(cudaStreamSynchronize(h->stream));

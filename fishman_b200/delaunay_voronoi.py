@@ -46,6 +46,15 @@ def _i(a):
     return a.ctypes.data_as(C.POINTER(C.c_int32))
 
 
+def pinned_empty(n):
+    """float64 array of n elements in page-locked host memory (fm_host_alloc); kept alive
+    for the life of the process."""
+    p = C.c_void_p()
+    if _lib.lib().fm_host_alloc(8 * int(n), C.byref(p)):
+        raise FishmanError("fm_host_alloc failed")
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(int(n),))
+
+
 class Mesh:
     def __init__(self, num_point=None, lon=None, lat=None, x=None, y=None, z=None, rank=0, size=1):
         """delaunay_voronoi_init: either lon/lat or x/y/z (DV:204-220)."""
@@ -94,6 +103,10 @@ class Mesh:
     # ---- the reference's call sequence
     def delaunay_triangulation(self):
         self._chk(_lib.lib().fm_triangulate(self._h))
+
+    def retriangulate(self, warm=True):
+        """Triangulation of the current (moved) generators; warm = repair by flips."""
+        self._chk(_lib.lib().fm_retriangulate(self._h, 1 if warm else 0))
 
     def voronoi_diagram(self, all=False):
         self._chk(_lib.lib().fm_voronoi(self._h, 1 if all else 0))
@@ -147,6 +160,13 @@ class Mesh:
     def set_generators(self, xyz):
         g = np.ascontiguousarray(np.asarray(xyz, dtype=np.float64).T)
         self._chk(_lib.lib().fm_set_generators(self._h, _d(g[0]), _d(g[1]), _d(g[2])))
+
+    def set_generators_soa(self, x, y, z):
+        """Three contiguous float64 arrays (e.g. pinned_empty): no host-side repacking."""
+        self._chk(_lib.lib().fm_set_generators(self._h, _d(x), _d(y), _d(z)))
+
+    def get_generators_soa(self, x, y, z):
+        self._chk(_lib.lib().fm_get_generators(self._h, _d(x), _d(y), _d(z)))
 
     # ---- Lloyd (SURVEY.md 7.3)
     def lloyd(self, rho=None, max_iter=1, tol=0.0, warm=True):

@@ -27,6 +27,7 @@
  */
 #ifndef FISHMAN_B200_H
 #define FISHMAN_B200_H
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -59,6 +60,11 @@ const char* fm_last_error(const fm_handle* h); /* h may be NULL: error of the la
 
 /* delaunay_triangulation()  DV:226-356 */
 int fm_triangulate(fm_handle* h);
+/* Triangulation of the CURRENT generators (after fm_lloyd / fm_set_generators).  warm != 0:
+ * keep the previous connectivity and repair it by flip rounds (falls back to a rebuild when
+ * a triangle turned over); warm == 0: rebuild from scratch.  No reference equivalent: the
+ * reference module is single-shot. */
+int fm_retriangulate(fm_handle* h, int32_t warm);
 /* sizes for the caller's buffers: T = 2N-4, E = 3N-6 (DV:413, DV:435) */
 int fm_counts(const fm_handle* h, int32_t* n_tri, int32_t* n_edge);
 /* get_DT: tri and adj are 3 x T column-major (Fortran tri(3,T)) */
@@ -95,6 +101,11 @@ int fm_generator_block(fm_handle* h, void** dx, void** dy, void** dz, int64_t* n
 int fm_get_generators(fm_handle* h, double* x, double* y, double* z);
 /* replace the generators (host -> device), keeping the internal order and topology */
 int fm_set_generators(fm_handle* h, const double* x, const double* y, const double* z);
+
+/* Page-locked host buffers for the arrays that cross the boundary (optional: any host
+ * pointer is accepted, pinned ones copy at full PCIe rate). */
+int fm_host_alloc(size_t bytes, void** out);
+int fm_host_free(void* p);
 
 /* Measurement support (bench.py): wall-clock of the device work between begin/end taken
  * with CUDA events on the handle's stream, and per-kernel accounting. */

@@ -1,0 +1,48 @@
+"""Builds and binds tests/emu/fm_emu.cpp: the kernel bodies of fishman_b200/csrc run
+thread by thread on the host.  TEST INFRASTRUCTURE ONLY (CPU logic tests); the
+product library has no host path."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "emu", "fm_emu.cpp")
+LIB = os.path.join(HERE, "emu", "libfm_emu.so")
+CSRC = os.path.join(HERE, "..", "fishman_b200", "csrc")
+_lib = None
+
+
+def build():
+    deps = [SRC] + [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
+    if (not os.path.exists(LIB)) or os.path.getmtime(LIB) < max(os.path.getmtime(d) for d in deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared",
+                               "-o", LIB, SRC, "-lm"])
+    return LIB
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(LIB)
+        L.fme_last_error.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def triangulate(xyz, sort=True):
+    """Returns (tri, adj, stats) with 1-based ids, through the emulated kernels."""
+    p = np.ascontiguousarray(xyz, dtype=np.float64)
+    n = len(p)
+    T = 2 * n - 4
+    tri = np.empty((T, 3), np.int32)
+    adj = np.empty((T, 3), np.int32)
+    st = np.zeros(4, np.int32)
+    ip = C.POINTER(C.c_int)
+    rc = lib().fme_triangulate(n, p.ctypes.data_as(C.POINTER(C.c_double)), tri.ctypes.data_as(ip),
+                               adj.ctypes.data_as(ip), st.ctypes.data_as(ip), 1 if sort else 0)
+    if rc:
+        raise RuntimeError(lib().fme_last_error().decode())
+    return tri, adj, dict(rounds=int(st[0]), subrounds=int(st[1]), flips=int(st[2]), max_active=int(st[3]))

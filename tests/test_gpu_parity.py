@@ -1,0 +1,233 @@
+"""GPU parity tests (-m gpu): the sm_100a library, called through the C ABI
+(ctypes binding of include/fishman_b200.h), against the CPU oracle
+(oracle/fishman_oracle.c, the restatement of the reference) and Qhull on the same
+seeded inputs.  Topology: canonical sorted triples bit-exact.
+Coordinates: 1e-12 (absolute on unit vectors = relative), per Lloyd step."""
+import numpy as np
+import pytest
+
+from tests import _check
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-12
+
+
+@pytest.fixture(scope="module")
+def fb():
+    import fishman_b200 as fb
+    return fb
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import oracle as O
+    O.build()
+    return O
+
+
+def _sets():
+    from fishman_b200 import points
+    return [("octa", np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1.0]])),
+            ("ico0", points.ico(0)), ("ico2", points.ico(2)), ("ico5", points.ico(5)),
+            ("u500", points.uniform(500, 3)), ("u10242", points.uniform(10242, 0)),
+            ("fib5000", points.fibonacci(5000, 0))]
+
+
+@pytest.mark.parametrize("name", [s[0] for s in _sets()])
+def test_dt_vd_against_oracle(fb, O, name):
+    p = dict(_sets())[name]
+    m = fb.Mesh.from_xyz(p)
+    m.delaunay_triangulation()
+    m.voronoi_diagram(all=True)
+    tri, adj = m.triangles()
+    _check.check_triangulation(p, tri, adj)
+    o = O.Oracle(p)
+    otri, _ = o.delaunay_triangulation()
+    occ, oll, ooff, ort, orn = o.voronoi_diagram()
+    if name not in ("octa", "ico0", "ico2", "ico5"):  # symmetric sets have cocircular quads: DT not unique
+        assert np.array_equal(_check.canonical(tri), _check.canonical(otri))
+        cc, ll = m.circumcentres()
+        assert _check.max_cc_diff(tri, cc, otri, occ) < TOL
+        assert _check.max_cc_diff(tri, ll, otri, oll) < 1e-9  # lon/lat: atan2 conditioning near the poles
+    off, rt, rn = m.rings()
+    _check.check_rings(p, tri, off, rt, rn)
+    if name not in ("octa", "ico0", "ico2", "ico5"):
+        assert np.array_equal(off, ooff)
+        (orn_r,) = _check.rotate_rings(ooff, orn)
+        assert np.array_equal(rn, orn_r)
+    de, vv, vc = m.edges()
+    assert len(de) == 3 * len(p) - 6
+    assert (de[:, 0] < de[:, 1]).all() and np.array_equal(de, vc)
+    # Voronoi edge k is the dual of Delaunay edge k: both triangles contain both cells (DV:435-460)
+    t0 = tri.astype(np.int64)
+    for col in range(2):
+        tt = t0[vv[:, col] - 1]
+        assert ((tt == de[:, [0]]).any(1) & (tt == de[:, [1]]).any(1)).all()
+    m.close()
+
+
+def test_icosahedral_degrees(fb):
+    """Bisected icosahedra: exactly 12 degree-5 cells, the rest degree-6."""
+    from fishman_b200 import points
+    for k in (1, 3, 5):
+        p = points.ico(k)
+        m = fb.Mesh.from_xyz(p)
+        m.delaunay_triangulation()
+        m.voronoi_diagram()
+        off, _, _ = m.rings()
+        deg = np.diff(off)
+        assert (deg == 5).sum() == 12 and (deg == 6).sum() == len(p) - 12
+        m.close()
+
+
+def test_qhull_163842(fb):
+    from scipy.spatial import ConvexHull
+    from fishman_b200 import points
+    p = points.uniform(163842, 0)
+    m = fb.Mesh.from_xyz(p)
+    m.delaunay_triangulation()
+    tri, adj = m.triangles()
+    _check.check_triangulation(p, tri, adj)
+    q = ConvexHull(p).simplices + 1
+    assert np.array_equal(_check.canonical(tri), _check.canonical(q))
+    m.close()
+
+
+def test_degenerate_latlon_grid(fb):
+    """Cocircular quads and collinear meridian points: the exact + SoS predicates must
+    still give a valid triangulation (the reference abstains / is history dependent here)."""
+    from fishman_b200 import points
+    p = points.latlon_grid(24, 48)
+    m = fb.Mesh.from_xyz(p)
+    m.delaunay_triangulation()
+    tri, adj = m.triangles()
+    _check.check_triangulation(p, tri, adj)
+    m.close()
+
+
+def test_lonlat_entry(fb):
+    from fishman_b200 import points
+    p = points.uniform(2000, 5)
+    lon, lat = np.arctan2(p[:, 1], p[:, 0]), np.arcsin(p[:, 2])
+    m1 = fb.Mesh(lon=lon, lat=lat)
+    m1.delaunay_triangulation()
+    q = np.stack([np.cos(lat) * np.cos(lon), np.cos(lat) * np.sin(lon), np.sin(lat)], 1)
+    m2 = fb.Mesh.from_xyz(q)
+    m2.delaunay_triangulation()
+    assert np.array_equal(_check.canonical(m1.triangles()[0]), _check.canonical(m2.triangles()[0]))
+    assert np.abs(m1.generators() - q).max() < 1e-15
+    m1.close(); m2.close()
+
+
+def test_errors(fb):
+    with pytest.raises(fb.FishmanError):
+        fb.Mesh.from_xyz(np.eye(3))
+    p = np.array([[1, 0, 0], [0, 1, 0], [0, 0, 1], [-1, 0, 0], [0, -1, 0], [0, 0, 1.0]])
+    with pytest.raises(fb.FishmanError, match="coincides"):
+        fb.Mesh.from_xyz(p)  # duplicate generator, DV:286-288
+    hemi = np.abs(np.random.default_rng(0).normal(size=(50, 3)))
+    hemi /= np.linalg.norm(hemi, axis=1)[:, None]
+    m = fb.Mesh.from_xyz(hemi)
+    with pytest.raises(fb.FishmanError):
+        m.delaunay_triangulation()
+    m.close()
+    m = fb.Mesh.from_xyz(np.random.default_rng(0).normal(size=(10, 3)))
+    with pytest.raises(fb.FishmanError):
+        m.voronoi_diagram()
+    m.close()
+
+
+@pytest.mark.parametrize("dens", ["uniform", "x4"])
+@pytest.mark.parametrize("warm", [False, True])
+def test_lloyd_steps_against_oracle(fb, O, dens, warm):
+    """k Lloyd iterations, both sides re-fed the same generators each step."""
+    from fishman_b200 import points
+    p = points.fibonacci(4000, 1)
+    rho_g = fb.density_uniform() if dens == "uniform" else fb.density_x4()
+    rho_o = O.density_uniform() if dens == "uniform" else O.density_x4()
+    m = fb.Mesh.from_xyz(p)
+    o = O.Oracle(p)
+    for it in range(5):
+        g0 = m.generators()
+        n_it, md = m.lloyd(rho_g, max_iter=1, warm=warm)
+        assert n_it == 1
+        o.set_generators(g0)
+        omd = o.lloyd_step(rho_o)
+        og = o.generators()
+        g1 = m.generators()
+        assert np.abs(g1 - og).max() < TOL
+        assert abs(md - omd) < TOL
+        assert np.abs(np.linalg.norm(g1, axis=1) - 1).max() < 4e-16
+    # the warm-repaired triangulation is the Delaunay triangulation of the current generators
+    st = m.stats()
+    assert (st["warm"] > 0) == warm
+    m.close()
+
+
+def test_warm_equals_cold_topology(fb):
+    from fishman_b200 import points
+    p = points.uniform(20000, 2)
+    m = fb.Mesh.from_xyz(p)
+    m.lloyd(max_iter=6, warm=True)
+    g = m.generators()
+    # warm: repair only (no centroid step) == cold triangulation of the same generators
+    m2 = fb.Mesh.from_xyz(g)
+    m2.delaunay_triangulation()
+    m.set_generators(g)
+    m.retriangulate(warm=True)
+    assert np.array_equal(_check.canonical(m.triangles()[0]), _check.canonical(m2.triangles()[0]))
+    assert m.stats()["warm"] >= 6
+    m.close(); m2.close()
+
+
+def test_lloyd_converges_and_quality(fb, O):
+    from fishman_b200 import points
+    p = points.uniform(2562, 4)
+    m = fb.Mesh.from_xyz(p)
+    it, md0 = m.lloyd(max_iter=1)
+    it, md = m.lloyd(max_iter=200, tol=0.0)
+    assert md < md0 / 10
+    m.delaunay_triangulation()
+    m.voronoi_diagram()
+    off, _, _ = m.rings()
+    deg = np.diff(off)
+    assert ((deg >= 5) & (deg <= 7)).mean() > 0.99
+    o = O.Oracle(m.generators())
+    o.delaunay_triangulation(); o.voronoi_diagram()
+    ac, at, sc, st = o.areas()
+    assert abs(sc - 4 * np.pi) < 1e-10 and abs(st - 4 * np.pi) < 1e-10  # MM:306, MM:320
+    assert ac.max() / ac.min() < 2.0
+    m.close()
+
+
+def test_full_size_properties(fb):
+    """C4 size (2,621,442): size-independent properties only."""
+    from fishman_b200 import points
+    p = points.fibonacci(2621442, 0)
+    m = fb.Mesh.from_xyz(p)
+    m.delaunay_triangulation()
+    tri, adj = m.triangles()
+    _check.check_triangulation(p, tri, adj)
+    # idempotence: warm repair of a Delaunay triangulation flips nothing
+    m.stats_reset()
+    m.retriangulate(warm=True)
+    assert m.stats()["flips"] == 0
+    m.voronoi_diagram()
+    off, rt, rn = m.rings()
+    _check.check_rings(p, tri, off, rt, rn)
+    # local Delaunay property on every edge, plain fp64 with the reference's eps rule (DV:2051-2061)
+    t0 = tri.astype(np.int64) - 1
+    a0 = adj.astype(np.int64) - 1
+    for k in range(3):
+        nb = t0[a0[:, k]]
+        mask = (nb != t0[:, [(k + 1) % 3]]) & (nb != t0[:, [(k + 2) % 3]])
+        d = p[nb[mask]]
+        v1, v2, v3 = p[t0[:, 0]], p[t0[:, 1]], p[t0[:, 2]]
+        det = np.einsum("ij,ij->i", v3 - d, np.cross(v2 - d, v1 - d))
+        assert (det <= 2.220446049250313e-16).all()
+    it, md = m.lloyd(max_iter=3, warm=True)
+    g = m.generators()
+    assert np.abs(np.linalg.norm(g, axis=1) - 1).max() < 4e-16
+    assert 0 < md < 0.01
+    m.close()
