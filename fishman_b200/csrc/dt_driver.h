@@ -108,6 +108,26 @@ int dt_bootstrap(B& be, DtCtx& c, int boot[4], char* msg, size_t msglen) {
       if (orient(p[a], p[b], p[d], id[a], id[b], id[d]) <= 0) ok = false;
     }
   }
+  if (!ok && c.n <= 64) {
+    // tiny sets: try every quadruple (Caratheodory: if the centre is inside the hull of
+    // the points, four of them already enclose it)
+    P3 q[64];
+    int qi[64];
+    for (int i = 0; i < c.n; i++) { q[i] = be.fetch_point(c, i); qi[i] = be.fetch_orig(c, i); }
+    for (int a = 0; a < c.n && !ok; a++)
+      for (int b = a + 1; b < c.n && !ok; b++)
+        for (int d = b + 1; d < c.n && !ok; d++)
+          for (int e = d + 1; e < c.n && !ok; e++) {
+            int s[4] = {a, b, d, e};
+            if (orient(q[s[0]], q[s[1]], q[s[2]], qi[s[0]], qi[s[1]], qi[s[2]]) < 0) { s[1] = d; s[2] = b; }
+            bool good = true;
+            for (int f = 0; f < 4 && good; f++) {
+              int u = s[F[f][0]], v = s[F[f][1]], w = s[F[f][2]];
+              good = orient(q[u], q[v], q[w], qi[u], qi[v], qi[w]) > 0;
+            }
+            if (good) { ok = true; for (int k = 0; k < 4; k++) boot[k] = s[k]; }
+          }
+  }
   if (!ok) {
     snprintf(msg, msglen,
              "bootstrap: no four points enclosing the sphere centre were found (points confined "

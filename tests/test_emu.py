@@ -1,0 +1,72 @@
+"""CPU logic tests of the Delaunay kernels: the per-thread bodies of
+fishman_b200/csrc/dt_kernels.cuh and the round driver dt_driver.h, executed thread by
+thread on the host (tests/emu/fm_emu.cpp), against the oracle, Qhull and the golden
+fixtures.  This checks the algorithm (votes, splits, flip rounds, exact predicates);
+the CUDA build of the same bodies is checked on the GPU by tests/test_gpu_parity.py."""
+import os
+
+import numpy as np
+import pytest
+
+from fishman_b200 import points
+from oracle import oracle as O
+from tests import _check, _emu
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.mark.parametrize("name", ["u300", "fib500", "u2000"])
+def test_emu_against_golden(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    tri, adj, st = _emu.triangulate(g["xyz"])
+    _check.check_triangulation(g["xyz"], tri, adj)
+    assert np.array_equal(_check.canonical(tri), g["tri"])
+
+
+@pytest.mark.parametrize("n,seed,sort", [(4, 0, True), (5, 1, True), (8, 1, False), (64, 3, True),
+                                         (1000, 4, False), (10242, 0, True), (40000, 5, True)])
+def test_emu_against_oracle(n, seed, sort):
+    p = points.uniform(n, seed)
+    if n == 4:  # four random points need not surround the centre; use a tetrahedron
+        p = np.array([[1, 1, 1], [1, -1, -1], [-1, 1, -1], [-1, -1, 1.0]]) / np.sqrt(3)
+    if n == 5:
+        p = np.concatenate([np.array([[1, 1, 1], [1, -1, -1], [-1, 1, -1], [-1, -1, 1.0]]) / np.sqrt(3),
+                            points.uniform(1, 1)])
+    tri, adj, st = _emu.triangulate(p, sort=sort)
+    _check.check_triangulation(p, tri, adj)
+    if n >= 64:
+        o = O.Oracle(p)
+        otri, _ = o.delaunay_triangulation()
+        assert np.array_equal(_check.canonical(tri), _check.canonical(otri))
+        assert st["rounds"] <= 4 * int(np.log2(n)) + 8  # one point per triangle per round: O(log n) rounds
+
+
+def test_emu_order_independent():
+    """SoS keys on the ORIGINAL ids, so the internal (Morton) order must not matter."""
+    p = points.ico(3)  # cocircular quads: only the tie-break decides
+    a = _check.canonical(_emu.triangulate(p, sort=True)[0])
+    b = _check.canonical(_emu.triangulate(p, sort=False)[0])
+    assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("maker", [lambda: points.latlon_grid(12, 24), lambda: points.ico(4),
+                                   lambda: np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1.0]])])
+def test_emu_degenerate_inputs(maker):
+    """Cocircular / collinear configurations: valid triangulation, locally Delaunay up to ties."""
+    p = maker()
+    tri, adj, st = _emu.triangulate(p)
+    _check.check_triangulation(p, tri, adj)
+    t0, a0 = tri.astype(np.int64) - 1, adj.astype(np.int64) - 1
+    for k in range(3):
+        nb = t0[a0[:, k]]
+        mask = (nb != t0[:, [(k + 1) % 3]]) & (nb != t0[:, [(k + 2) % 3]])
+        d = p[nb[mask]]
+        v1, v2, v3 = p[t0[:, 0]], p[t0[:, 1]], p[t0[:, 2]]
+        det = np.einsum("ij,ij->i", v3 - d, np.cross(v2 - d, v1 - d))  # DV:2051-2053
+        assert (det <= 1e-14).all()
+
+
+def test_emu_hemisphere_fails_cleanly():
+    hemi = np.abs(points.uniform(40, 0))
+    with pytest.raises(RuntimeError, match="bootstrap"):
+        _emu.triangulate(hemi)
