@@ -1,0 +1,184 @@
+! fishman_gpu_c.F90 -- ISO_C_BINDING view of include/fishman_b200.h.
+!
+! This is the thin bind(C) layer the north star asks for: the Fortran host
+! (gen_mesh, the output_interface plug-in contract, mpas_mesh_mod) stays as it is
+! and the bodies of delaunay_voronoi_init / delaunay_triangulation /
+! voronoi_diagram in src/delaunay_voronoi_mod.F90 call these entry points instead
+! of running the serial algorithm (see INTEGRATION.md for the replacement bodies).
+!
+! NOT COMPILED IN THIS REPOSITORY'S IMAGE: no Fortran compiler exists there.  The
+! signatures below are checked mechanically against the C header by
+! tests/test_fortran_binding.py (names, argument counts, value/reference passing).
+module fishman_gpu_c
+
+  use, intrinsic :: iso_c_binding
+
+  implicit none
+
+  private
+  public :: fm_density
+  public :: fm_create, fm_create_lonlat, fm_create_dist, fm_destroy, fm_last_error
+  public :: fm_triangulate, fm_retriangulate, fm_counts, fm_get_triangles
+  public :: fm_voronoi, fm_get_circumcentres, fm_get_rings, fm_get_edges
+  public :: fm_lloyd, fm_lloyd_local, fm_generator_block
+  public :: fm_get_generators, fm_set_generators
+  public :: fm_error_message
+
+  ! typedef struct fm_density { int32_t kind; double cx, cy, cz, beta, alpha, gamma; }
+  type, bind(C) :: fm_density
+    integer(c_int32_t) :: kind = 0
+    real(c_double) :: cx = 0.0d0, cy = 0.0d0, cz = 1.0d0
+    real(c_double) :: beta = 0.0d0, alpha = 1.0d0, gamma = 1.0d0
+  end type fm_density
+
+  interface
+
+    ! delaunay_voronoi_init(num_point, x=, y=, z=), DV:188-224
+    integer(c_int) function fm_create(n, x, y, z, h) bind(C, name='fm_create')
+      import :: c_int, c_int32_t, c_double, c_ptr
+      integer(c_int32_t), value :: n
+      real(c_double), intent(in) :: x(*), y(*), z(*)
+      type(c_ptr), intent(out) :: h
+    end function fm_create
+
+    ! delaunay_voronoi_init(num_point, lon=, lat=), DV:204-211
+    integer(c_int) function fm_create_lonlat(n, lon, lat, h) bind(C, name='fm_create_lonlat')
+      import :: c_int, c_int32_t, c_double, c_ptr
+      integer(c_int32_t), value :: n
+      real(c_double), intent(in) :: lon(*), lat(*)
+      type(c_ptr), intent(out) :: h
+    end function fm_create_lonlat
+
+    integer(c_int) function fm_create_dist(n, x, y, z, rank, size, h) bind(C, name='fm_create_dist')
+      import :: c_int, c_int32_t, c_double, c_ptr
+      integer(c_int32_t), value :: n, rank, size
+      real(c_double), intent(in) :: x(*), y(*), z(*)
+      type(c_ptr), intent(out) :: h
+    end function fm_create_dist
+
+    subroutine fm_destroy(h) bind(C, name='fm_destroy')
+      import :: c_ptr
+      type(c_ptr), value :: h
+    end subroutine fm_destroy
+
+    type(c_ptr) function fm_last_error(h) bind(C, name='fm_last_error')
+      import :: c_ptr
+      type(c_ptr), value :: h
+    end function fm_last_error
+
+    ! delaunay_triangulation(), DV:226-356
+    integer(c_int) function fm_triangulate(h) bind(C, name='fm_triangulate')
+      import :: c_int, c_ptr
+      type(c_ptr), value :: h
+    end function fm_triangulate
+
+    integer(c_int) function fm_retriangulate(h, warm) bind(C, name='fm_retriangulate')
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), value :: warm
+    end function fm_retriangulate
+
+    integer(c_int) function fm_counts(h, n_tri, n_edge) bind(C, name='fm_counts')
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: n_tri, n_edge
+    end function fm_counts
+
+    ! tri(3,T), adj(3,T): Fortran column-major = the C layout
+    integer(c_int) function fm_get_triangles(h, tri, adj) bind(C, name='fm_get_triangles')
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: tri(3, *), adj(3, *)
+    end function fm_get_triangles
+
+    ! voronoi_diagram(all), DV:358-585
+    integer(c_int) function fm_voronoi(h, all) bind(C, name='fm_voronoi')
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), value :: all
+    end function fm_voronoi
+
+    integer(c_int) function fm_get_circumcentres(h, xyz, lonlat) bind(C, name='fm_get_circumcentres')
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      real(c_double), intent(out) :: xyz(3, *), lonlat(2, *)
+    end function fm_get_circumcentres
+
+    integer(c_int) function fm_get_rings(h, off, ring_tri, ring_nbr) bind(C, name='fm_get_rings')
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: off(*), ring_tri(*), ring_nbr(*)
+    end function fm_get_rings
+
+    integer(c_int) function fm_get_edges(h, de, ve_vvt, ve_vc) bind(C, name='fm_get_edges')
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: de(2, *), ve_vvt(2, *), ve_vc(2, *)
+    end function fm_get_edges
+
+    ! Lloyd loop: no reference procedure (SURVEY.md F1)
+    integer(c_int) function fm_lloyd(h, rho, max_iter, tol, warm, iters, max_disp) bind(C, name='fm_lloyd')
+      import :: c_int, c_int32_t, c_double, c_ptr, fm_density
+      type(c_ptr), value :: h
+      type(fm_density), intent(in) :: rho
+      integer(c_int32_t), value :: max_iter, warm
+      real(c_double), value :: tol
+      integer(c_int32_t), intent(out) :: iters
+      real(c_double), intent(out) :: max_disp
+    end function fm_lloyd
+
+    integer(c_int) function fm_lloyd_local(h, rho, warm, max_disp) bind(C, name='fm_lloyd_local')
+      import :: c_int, c_int32_t, c_double, c_ptr, fm_density
+      type(c_ptr), value :: h
+      type(fm_density), intent(in) :: rho
+      integer(c_int32_t), value :: warm
+      real(c_double), intent(out) :: max_disp
+    end function fm_lloyd_local
+
+    integer(c_int) function fm_generator_block(h, dx, dy, dz, n_padded, begin, count) &
+        bind(C, name='fm_generator_block')
+      import :: c_int, c_int64_t, c_ptr
+      type(c_ptr), value :: h
+      type(c_ptr), intent(out) :: dx, dy, dz
+      integer(c_int64_t), intent(out) :: n_padded, begin, count
+    end function fm_generator_block
+
+    integer(c_int) function fm_get_generators(h, x, y, z) bind(C, name='fm_get_generators')
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      real(c_double), intent(out) :: x(*), y(*), z(*)
+    end function fm_get_generators
+
+    integer(c_int) function fm_set_generators(h, x, y, z) bind(C, name='fm_set_generators')
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      real(c_double), intent(in) :: x(*), y(*), z(*)
+    end function fm_set_generators
+
+  end interface
+
+contains
+
+  ! C string of fm_last_error -> Fortran string (for log_error)
+  function fm_error_message(h) result(msg)
+    type(c_ptr), intent(in) :: h
+    character(:), allocatable :: msg
+    type(c_ptr) :: p
+    character(kind=c_char), pointer :: s(:)
+    integer :: n
+    p = fm_last_error(h)
+    if (.not. c_associated(p)) then
+      msg = 'unknown error'
+      return
+    end if
+    call c_f_pointer(p, s, [512])
+    n = 0
+    do while (n < 512)
+      if (s(n + 1) == c_null_char) exit
+      n = n + 1
+    end do
+    allocate(character(n) :: msg)
+    msg = transfer(s(1:n), msg)
+  end function fm_error_message
+
+end module fishman_gpu_c
