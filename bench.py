@@ -32,15 +32,13 @@ REF_SAMPLE_N = 163842   # --impl reference: each step is one iteration at this s
 
 # Algorithmic bytes per work item of each kernel (DESIGN.md "Kernels and rooflines").
 ALG_BYTES = {
-    "locate_vote": 80,       # point xyz 24 + loc r/w 8 + orig 4 + one triangle row 16+16 + vote 8 + 4 pad
-    "split_flag": 12, "split13": 120,
-    "flip_check": 76,        # tri 16 + adj 16 + amortised own vertices 14 + 3 opposite ids/coords amortised 14 + flip_edge 4 + queue 4 + vote 8
-    "flip_mark": 24, "flip22": 96, "flip_patch": 24,
-    "validate": 30, "queue_all": 8,
-    "circumcentre": 48,
-    "vertex_to_tri": 28,
-    "centroid_update": 124,
-    "cub_scan": 8,
+    "locate_vote": 80,       # point record 32 + loc r/w 8 + one triangle row tri+adj 32 + vote 8
+    "split_flag": 12, "split13": 128, "cub_scan": 8,
+    "flip_loop": 0,          # cooperative kernel: all flip sub-rounds of a round (latency bound, no byte model)
+    "sweep": 80,             # per triangle: tri 16 + adj 16 + vertex records amortised 32*N/T = 16 + circumcentre write 32
+    "circumcentre": 64,      # tri 16 + vertex records amortised 16 + write 32
+    "centroid_update": 156,  # per cell: record r/w 32+24 + v2t 4 + adj rows amortised 16*T/N = 32 + circumcentres amortised 32*T/N = 64
+    "validate": 32,
 }
 
 
@@ -53,50 +51,61 @@ def peaks():
 
 
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """Samples SM clock and throttle reasons through NVML from a thread while the timed
+    region runs (the ctypes calls into the library release the GIL).  ~1 ms period: the timed
+    region of a warm run is only tens of ms, far shorter than one nvidia-smi -lms tick."""
 
     def __init__(self, index):
-        self.rows, self.proc, self.index = [], None, index
+        self.index, self.rows, self.stop_flag, self.th, self.err = index, [], False, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                try:
+                    phys = int(vis.split(",")[index])
+                except ValueError:
+                    phys = index
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys)
+        except Exception as e:  # noqa: BLE001
+            self.nv, self.err = None, repr(e)
+
+    def _run(self):
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(
+                    nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.rows.append((sm, rs))
+            except Exception as e:  # noqa: BLE001
+                self.err = repr(e)
+                return
+            time.sleep(0.001)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=self._read, daemon=True)
+        if self.nv:
+            self.th = threading.Thread(target=self._run, daemon=True)
             self.th.start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append(line.strip())
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            f = [c.strip() for c in r.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        if not self.nv:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [f"nvml unavailable: {self.err}"]}
+        self.stop_flag = True
+        self.th.join(timeout=2)
+        nv = self.nv
+        mx = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                "hw_power_brake": 0x80}
+        seen = set()
+        for _, rs in self.rows:
+            for k, b in bits.items():
+                if rs & b:
+                    seen.add(k)
+        sm = [r[0] for r in self.rows]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(mx), "samples": len(sm),
+                "reasons": sorted(seen)}
 
 
 def make_points(n):
@@ -182,13 +191,12 @@ def run_gpu(args):
     m = fb.Mesh.from_xyz(p, rank=rank, size=world)
     gather = None
     if world > 1:
-        (px, py, pz), npad, beg, cnt = m.generator_block()
-        full = [torch.as_tensor(_DevPtr(q, npad), device=f"cuda:{local}") for q in (px, py, pz)]
+        ptr, npad, beg, cnt = m.generator_block()
+        full = torch.as_tensor(_DevPtr(ptr, 4 * npad), device=f"cuda:{local}")  # 32-byte records as 4 doubles
         mdt = torch.zeros(1, dtype=torch.float64, device=f"cuda:{local}")
 
         def gather(md):
-            for t in full:
-                dist.all_gather_into_tensor(t, t[beg:beg + cnt])
+            dist.all_gather_into_tensor(full, full[4 * beg:4 * (beg + cnt)])  # in place: one collective per iteration
             mdt[0] = md
             dist.all_reduce(mdt, op=dist.ReduceOp.MAX)
             return float(mdt.item())  # host sync: the next iteration may start
@@ -299,8 +307,8 @@ def run_gpu(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="warm", choices=["warm", "cold"])
     ap.add_argument("--n", type=int, default=N_C4)

@@ -50,7 +50,7 @@ def lib():
     L.fm_get_edges.argtypes = [vp, ip, ip, ip]
     L.fm_lloyd.argtypes = [vp, C.POINTER(Density), i32, C.c_double, i32, ip, dp]
     L.fm_lloyd_local.argtypes = [vp, C.POINTER(Density), i32, dp]
-    L.fm_generator_block.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), i64p, i64p, i64p]
+    L.fm_generator_block.argtypes = [vp, C.POINTER(vp), i64p, i64p, i64p]
     L.fm_get_generators.argtypes = [vp, dp, dp, dp]
     L.fm_set_generators.argtypes = [vp, dp, dp, dp]
     L.fm_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]

@@ -12,6 +12,9 @@
 //   Backend::fetch_point(ctx, i)          coordinates of point i on the host
 //   Backend::fetch_orig(ctx, i)
 //   Backend::write_tris(ctx, t0, cnt, tri, adj)
+//   Backend::flip_loop(ctx, list, cur, skip_check, stamp, stats, msg, len, nact_hint)
+//                                         flip sub-rounds until the queue is empty; nact_hint =
+//                                         length of the first queue when the host knows it, else -1
 //
 // Replaces: the bootstrap get_three_DVT_indices / init_DTs
 // (/root/reference/src/delaunay_voronoi_mod.F90:595-694) and the loop structure
@@ -150,29 +153,36 @@ int dt_bootstrap(B& be, DtCtx& c, int boot[4], char* msg, size_t msglen) {
   return 0;
 }
 
-// Flip sub-rounds until the queue runs dry.  cur holds nact queued triangles
-// (queued with stamp *stamp).  Returns 0 or 1 (msg filled).
+// Flip sub-rounds until the queue runs dry, host-driven (one launch per phase).  The
+// current queue is list[cur] with its length in counters[cur]; *stamp is the stamp it was
+// queued with.  skip_check: the first sub-round's check phase was already done by the
+// producer of the queue (KSweep).  This generic form serves the CPU logic tests; the CUDA
+// backend runs the same four bodies inside one cooperative kernel (Backend::flip_loop).
 template <class B>
-int dt_flip_loop(B& be, DtCtx& c, int* cur, int* nxt, int nact, int* stamp, DtStats* st, char* msg,
-                 size_t msglen) {
-  int zero[4] = {0, 0, 0, 0}, host[4];
-  while (nact > 0) {
+int dt_flip_loop_host(B& be, DtCtx& c, int* list[2], int cur, bool skip_check, int* stamp, DtStats* st,
+                      char* msg, size_t msglen, int /*nact_hint*/ = -1) {
+  int host[8];
+  for (;;) {
+    be.read_ints(host, c.counters, 8);
+    int nact = host[cur];
+    st->flips = host[2];
+    if (nact == 0) break;
     st->subrounds++;
     if (nact > st->max_active) st->max_active = nact;
-    be.write_ints(c.counters, zero, 1);
     c.stamp = *stamp;
-    c.active = cur;
+    c.active = list[cur];
     c.n_active = nact;
-    c.next_active = nxt;
-    be.template launch<KCheck>(c, nact);
+    c.next_active = list[cur ^ 1];
+    c.qcount = c.counters + (cur ^ 1);
+    if (!skip_check) be.template launch<KCheck>(c, nact);
+    skip_check = false;
     be.template launch<KMark>(c, nact);
     be.template launch<KFlip>(c, nact);
     be.template launch<KPatch>(c, nact);
-    be.read_ints(host, c.counters, 4);
-    nact = host[0];
-    st->flips = host[2];
+    int zero = 0;
+    be.write_ints(c.counters + cur, &zero, 1);
     (*stamp)++;
-    int* tmp = cur; cur = nxt; nxt = tmp;
+    cur ^= 1;
     if (*stamp > (1 << 28)) {
       snprintf(msg, msglen, "flip rounds did not terminate");
       return 1;
@@ -191,8 +201,9 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, cha
   int remaining = c.n - 4;
   c.n_tri = 4;
   memset(st, 0, sizeof *st);
-  int zero[4] = {0, 0, 0, 0}, host[4];
-  be.write_ints(c.counters, zero, 4);
+  int zero[8] = {0, 0, 0, 0, 0, 0, 0, 0}, host[8];
+  int* list[2] = {listA, listB};
+  be.write_ints(c.counters, zero, 7);
   while (remaining > 0) {
     st->rounds++;
     be.fill64(c.winner, kNone64, (size_t)c.n_tri);
@@ -208,33 +219,35 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, cha
       snprintf(msg, msglen, "no triangle accepted a point although %d remain", remaining);
       return 1;
     }
-    be.write_ints(c.counters, zero, 1);
     c.stamp = *stamp;
-    c.next_active = listA;
+    c.next_active = list[0];
+    c.qcount = c.counters;
     be.template launch<KSplit>(c, c.n_tri);
     remaining -= nsplit;
     c.n_tri += 2 * nsplit;
-    if (dt_flip_loop(be, c, listA, listB, 3 * nsplit, stamp, st, msg, msglen)) return 1;
+    if (be.flip_loop(c, list, 0, false, stamp, st, msg, msglen, 3 * nsplit)) return 1;
   }
+  be.read_ints(host, c.counters, 8);
+  st->flips = host[2];
+  if (host[5]) { st->subrounds = host[5]; st->max_active = host[6]; }
   return 0;
 }
 
-// Warm restart: the connectivity of the previous triangulation with moved
-// vertices.  Returns 0 repaired, 2 when a triangle turned over (caller rebuilds
-// from scratch), 1 on error.
+// Warm restart: the connectivity of the previous triangulation with moved vertices, repaired
+// by flips.  Launches only (no host synchronisation): counters[3] > 0 afterwards means a
+// triangle turned over -- the flip loop then did nothing and the caller must rebuild.
 template <class B>
-int dt_repair(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, char* msg,
-              size_t msglen) {
-  int zero[4] = {0, 0, 0, 0}, host[4];
+int dt_repair_async(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, char* msg,
+                    size_t msglen) {
+  int zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int* list[2] = {listA, listB};
   memset(st, 0, sizeof *st);
-  be.write_ints(c.counters, zero, 4);
+  be.write_ints(c.counters, zero, 7);
   c.stamp = *stamp;
-  c.next_active = listA;
-  be.template launch<KValidate>(c, c.n_tri);
-  be.template launch<KQueueAll>(c, c.n_tri);
-  be.read_ints(host, c.counters, 4);
-  if (host[3] > 0) return 2;
-  return dt_flip_loop(be, c, listA, listB, c.n_tri, stamp, st, msg, msglen);
+  c.next_active = list[0];
+  c.qcount = c.counters;
+  be.template launch<KSweep>(c, c.n_tri);
+  return be.flip_loop(c, list, 0, true, stamp, st, msg, msglen, -1);
 }
 
 }  // namespace fm

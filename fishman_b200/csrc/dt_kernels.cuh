@@ -52,10 +52,18 @@ static const u64 kNone64 = ~0ULL;
 // error bits reported through DtCtx::err
 enum { FM_E_WALK = 1, FM_E_TOPOLOGY = 2, FM_E_OVERFLOW = 4 };
 
+// Generator record: 32 bytes = one DRAM sector, so that a vertex gather costs one sector
+// instead of four (x, y, z, id in separate arrays).  id = original 0-based id (SoS key).
+struct alignas(16) P4 {
+  double x, y, z;
+  long long id;
+};
+
 struct DtCtx {
   int n;                       // points
-  const double *x, *y, *z;     // internal (space-filling-curve) order
-  const int* orig;             // original 0-based id of internal point i (SoS key)
+  P4* pts;                     // internal (space-filling-curve) order
+  int* v2t;                    // per vertex: SOME incident triangle (ring start), kept by split/flip
+  P4* cc;                      // circumcentres per triangle, maintained by sweep/flip when non-null
   I4* tri;                     // vertices (x,y,z), CCW seen from outside; w unused
   I4* adj;                     // adj[k] = (neighbour << 2 | its edge index) across the edge
                                // opposite vertex k (the reference's adjDT(k), DV:656-669)
@@ -65,6 +73,8 @@ struct DtCtx {
   int n_tri;                   // triangles alive at the start of the round
   // flip rounds
   int stamp;                   // global sub-round counter (>= 1)
+  const int* stamp_dev;        // when non-null the device-resident stamp (counters[7]) overrides
+                               // `stamp` at kernel entry: the flip loop advances it on the device
   u64* vote;                   // per triangle: (~stamp << 32 | voter) claimed by atomicMin
   int* flip_edge;              // per active triangle: edge it wants to flip, -1 none
   int* role;                   // per triangle: stamp << 2 | (1 winner, 2 partner)
@@ -73,11 +83,32 @@ struct DtCtx {
   const int* active;           // triangles to check this sub-round
   int n_active;
   int* next_active;            // queue for the next sub-round
-  int* counters;               // [0] next_active length, [1] splits, [2] flips, [3] walk steps
+  int* qcount;                 // length of next_active (one of counters[0], counters[1])
+  int* counters;               // [0],[1] queue lengths (ping-pong), [2] flips, [3] turned-over
+                               // triangles, [4] splits, [5] flip sub-rounds, [6] largest queue,
+                               // [7] next unused stamp (device-resident copy)
   int* err;
 };
 
-FM_HD inline P3 ldp(const DtCtx& c, int i) { return P3{c.x[i], c.y[i], c.z[i]}; }
+FM_HD inline P3 ldp(const DtCtx& c, int i) { const P4& q = c.pts[i]; return P3{q.x, q.y, q.z}; }
+// point and SoS id with two 16-byte loads of the same sector
+FM_HD inline P3 ldv(const DtCtx& c, int i, int& id) {
+  P4 q = c.pts[i];
+  id = (int)q.id;
+  return P3{q.x, q.y, q.z};
+}
+// circumcentre of the CCW triangle (a,b,c): normalised (b-a) x (c-a), DV:1335-1344
+FM_HD inline P3 circumcentre(const P3& a, const P3& b, const P3& c, bool& degenerate) {
+  double e3x = b.x - a.x, e3y = b.y - a.y, e3z = b.z - a.z;
+  double e2x = c.x - a.x, e2y = c.y - a.y, e2z = c.z - a.z;
+  double nx = e3y * e2z - e3z * e2y;  // cross_product, src/math_mod.F90:12-22
+  double ny = e3z * e2x - e3x * e2z;
+  double nz = e3x * e2y - e3y * e2x;
+  double l = sqrt(nx * nx + ny * ny + nz * nz);
+  degenerate = l < 2.220446049250313e-16;  // "collinear", DV:1339-1341
+  if (degenerate) l = 1.0;
+  return P3{nx / l, ny / l, nz / l};
+}
 FM_HD inline int enc(int t, int e) { return (t << 2) | e; }
 FM_HD inline int geti(const I4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
 FM_HD inline void seti(I4& v, int k, int val) {
@@ -109,7 +140,7 @@ FM_HD inline u64 morton_key(double x, double y, double z) {
 
 FM_HD inline void queue_active(const DtCtx& c, int t, int stamp) {
   if (FM_ATOMIC_EXCH32(&c.amark[t], stamp) != stamp) {
-    int pos = FM_ATOMIC_ADD32(&c.counters[0], 1);
+    int pos = FM_ATOMIC_ADD32(c.qcount, 1);
     c.next_active[pos] = t;
   }
 }
@@ -123,14 +154,14 @@ struct KLocateVote {
   FM_HD static void run(const DtCtx& c, int p) {
     int t = c.loc[p];
     if (t < 0) return;
-    P3 q = ldp(c, p);
-    int qi = c.orig[p];
+    int qi;
+    P3 q = ldv(c, p, qi);
     int from = -1, steps = 0;
     for (;;) {
       I4 v = c.tri[t];
       I4 a = c.adj[t];
-      P3 pa = ldp(c, v.x), pb = ldp(c, v.y), pc = ldp(c, v.z);
-      int ia = c.orig[v.x], ib = c.orig[v.y], ic = c.orig[v.z];
+      int ia, ib, ic;
+      P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
       int next = -1;
       // edge opposite vertex k is (v[k+1], v[k+2]); q must be on its left
       if ((a.x >> 2) != from && orient(pb, pc, q, ib, ic, qi) < 0) next = a.x >> 2;
@@ -189,10 +220,12 @@ struct KSplit {
     c.tri[s2] = I4{v.z, v.x, p, 0};
     c.adj[s2] = I4{enc(t, 1), enc(s1, 0), outer[1], 0};
     c.loc[p] = -1;
+    c.v2t[p] = t;
+    c.v2t[v.z] = s1;  // the only vertex that left slot t
     queue_active(c, t, c.stamp);
     queue_active(c, s1, c.stamp);
     queue_active(c, s2, c.stamp);
-    FM_ATOMIC_ADD32(&c.counters[1], 1);
+    FM_ATOMIC_ADD32(&c.counters[4], 1);
   }
 };
 
@@ -211,19 +244,57 @@ struct KCheck {
     int t = c.active[i];
     I4 v = c.tri[t];
     I4 a = c.adj[t];
-    P3 pa = ldp(c, v.x), pb = ldp(c, v.y), pc = ldp(c, v.z);
-    int ia = c.orig[v.x], ib = c.orig[v.y], ic = c.orig[v.z];
+    int ia, ib, ic, idd;
+    P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
     int fe = -1;
     for (int k = 0; k < 3; k++) {
       int ne = geti(a, k), n = ne >> 2, e = ne & 3;
       int d = geti(c.tri[n], e);
-      if (incircle(pa, pb, pc, ldp(c, d), ia, ib, ic, c.orig[d]) > 0) { fe = k; break; }
+      P3 pd = ldv(c, d, idd);
+      if (incircle(pa, pb, pc, pd, ia, ib, ic, idd) > 0) { fe = k; break; }
     }
     c.flip_edge[t] = fe;
     if (fe >= 0) {
       u64 key = vote_key(c.stamp, t);
       FM_ATOMIC_MIN64(&c.vote[t], key);
       FM_ATOMIC_MIN64(&c.vote[geti(a, fe) >> 2], key);
+    }
+  }
+};
+
+// Warm restart, first sub-round: ONE pass over all triangles that (a) counts triangles that
+// turned over when the generators moved (counters[3]; any -> the caller rebuilds), (b) tests
+// every edge once -- from its lower-numbered triangle -- and claims violated ones exactly as
+// KCheck does, queueing the claimant for the mark/flip/patch phases, and (c) refreshes the
+// circumcentre of every triangle (flips refresh theirs).  Replaces validate + queue_all +
+// flip_check over T + circumcentre: the three vertices are gathered once.
+struct KSweep {
+  FM_HD static void run(const DtCtx& c, int t) {
+    I4 v = c.tri[t];
+    I4 a = c.adj[t];
+    int ia, ib, ic, idd;
+    P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
+    if (orient(pa, pb, pc, ia, ib, ic) <= 0) FM_ATOMIC_ADD32(&c.counters[3], 1);
+    int fe = -1;
+    for (int k = 0; k < 3; k++) {
+      int ne = geti(a, k), n = ne >> 2, e = ne & 3;
+      if (n < t) continue;
+      int d = geti(c.tri[n], e);
+      P3 pd = ldv(c, d, idd);
+      if (incircle(pa, pb, pc, pd, ia, ib, ic, idd) > 0) { fe = k; break; }
+    }
+    if (fe >= 0) {
+      c.flip_edge[t] = fe;
+      u64 key = vote_key(c.stamp, t);
+      FM_ATOMIC_MIN64(&c.vote[t], key);
+      FM_ATOMIC_MIN64(&c.vote[geti(a, fe) >> 2], key);
+      queue_active(c, t, c.stamp);
+    }
+    if (c.cc) {
+      bool dg;
+      P3 cc = circumcentre(pa, pb, pc, dg);
+      if (dg) *c.err |= FM_E_TOPOLOGY;
+      c.cc[t] = P4{cc.x, cc.y, cc.z, 0};
     }
   }
 };
@@ -292,6 +363,16 @@ struct KFlip {
     c.adj[t] = I4{outer[2], enc(n, 2), outer[0], 0};
     c.tri[n] = I4{va, vd, vc, 0};
     c.adj[n] = I4{outer[3], outer[1], enc(t, 1), 0};
+    c.v2t[vb] = t;  // b left slot n, c left slot t (a and d only gained a triangle)
+    c.v2t[vc] = n;
+    if (c.cc) {
+      P3 pa = ldp(c, va), pb = ldp(c, vb), pc = ldp(c, vc), pd = ldp(c, vd);
+      bool dg1, dg2;
+      P3 c1 = circumcentre(pa, pb, pd, dg1), c2 = circumcentre(pa, pd, pc, dg2);
+      if (dg1 || dg2) *c.err |= FM_E_TOPOLOGY;
+      c.cc[t] = P4{c1.x, c1.y, c1.z, 0};
+      c.cc[n] = P4{c2.x, c2.y, c2.z, 0};
+    }
     queue_active(c, t, c.stamp + 1);
     queue_active(c, n, c.stamp + 1);
     FM_ATOMIC_ADD32(&c.counters[2], 1);
@@ -320,18 +401,14 @@ struct KPatch {
 // After the generators moved (Lloyd), the old connectivity is still a valid
 // triangulation as long as no triangle turned over; it is then repaired by flip
 // rounds alone instead of being rebuilt.  KValidate counts triangles that are
-// not strictly CCW any more (counters[3]); KQueueAll queues every triangle.
+// not strictly CCW any more (counters[3]).
 struct KValidate {
   FM_HD static void run(const DtCtx& c, int t) {
     I4 v = c.tri[t];
-    if (orient(ldp(c, v.x), ldp(c, v.y), ldp(c, v.z), c.orig[v.x], c.orig[v.y], c.orig[v.z]) <= 0)
+    int ia, ib, ic;
+    P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
+    if (orient(pa, pb, pc, ia, ib, ic) <= 0)
       FM_ATOMIC_ADD32(&c.counters[3], 1);
-  }
-};
-struct KQueueAll {
-  FM_HD static void run(const DtCtx& c, int t) {
-    c.next_active[t] = t;
-    c.amark[t] = c.stamp;
   }
 };
 

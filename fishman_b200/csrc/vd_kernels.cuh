@@ -1,14 +1,11 @@
 // vd_kernels.cuh -- per-thread bodies of the Voronoi / Lloyd kernels.
 //
 //   KCircum     circumcentres            DV:379-391, calc_circumcircle DV:1323-1348
-//   KV2T        one incident triangle per vertex (the reference's DVT%incDT head)
 //   KDegree / KRingFill   CSR vertex rings   extract_incident_DT_and_linked_DVT DV:704-743,
 //                                             cell rings DV:394-409
 //   KCentroid   density-weighted centroid + generator update + displacement
 //               (no reference code: SURVEY.md section 7.3 is the specification,
 //               restated on the CPU in oracle/fishman_oracle.c fo_centroids)
-//   KValidate   orientation check of every triangle after the generators moved
-//   KQueueAll   puts every triangle on the flip queue (warm restart)
 // "DV" = /root/reference/src/delaunay_voronoi_mod.F90.
 #pragma once
 #include <string.h>
@@ -40,18 +37,18 @@ struct Density {   // same layout as fm_density in include/fishman_b200.h
 
 struct VdCtx {
   int n, n_tri;
-  double *x, *y, *z;          // generators, internal order (updated in place by KCentroid)
-  const int* orig;            // internal -> original id
+  P4* pts;                    // generators, internal order (x,y,z updated in place by the Lloyd kernel)
   const I4* tri;
   const I4* adj;
-  double *ccx, *ccy, *ccz;    // circumcentres per triangle
+  P4* cc;                     // circumcentres per triangle (w unused)
   double *cclon, *cclat;      // optional (may be null)
-  int* v2t;                   // per vertex: lowest incident triangle
+  const int* v2t;             // per vertex: some incident triangle
   int* deg;                   // per ORIGINAL id: ring length, then its exclusive scan
   int *ring_tri, *ring_nbr;   // CSR payload, 1-based output ids
   Density rho;
   int cell_begin, cell_end;   // range of internal cells this rank updates
   u64* maxdisp;               // bits of the largest chord displacement (>= 0, so ordered)
+  const int* abort_flag;      // when non-null and != 0 the Lloyd kernel does nothing
   int* err;
 };
 
@@ -62,31 +59,17 @@ static const double kPi2 = 6.283185307179586476925287;
 struct KCircum {
   FM_HD static void run(const VdCtx& c, int t) {
     I4 v = c.tri[t];
-    double ax = c.x[v.x], ay = c.y[v.x], az = c.z[v.x];
-    double e3x = c.x[v.y] - ax, e3y = c.y[v.y] - ay, e3z = c.z[v.y] - az;
-    double e2x = c.x[v.z] - ax, e2y = c.y[v.z] - ay, e2z = c.z[v.z] - az;
-    double nx = e3y * e2z - e3z * e2y;  // cross_product, src/math_mod.F90:12-22
-    double ny = e3z * e2x - e3x * e2z;
-    double nz = e3x * e2y - e3y * e2x;
-    double l = sqrt(nx * nx + ny * ny + nz * nz);
-    if (l < kEps) { *c.err |= FM_E_TOPOLOGY; l = 1.0; }  // "collinear", DV:1339-1341
-    nx /= l; ny /= l; nz /= l;
-    c.ccx[t] = nx; c.ccy[t] = ny; c.ccz[t] = nz;
+    const P4 &qa = c.pts[v.x], &qb = c.pts[v.y], &qc = c.pts[v.z];
+    bool dg;
+    P3 n = circumcentre(P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, P3{qc.x, qc.y, qc.z}, dg);
+    if (dg) *c.err |= FM_E_TOPOLOGY;
+    c.cc[t] = P4{n.x, n.y, n.z, 0};
     if (c.cclon) {  // inverse_cartesian_transform, src/sphere_geometry_mod.F90:112-121
-      double lon = atan2(ny, nx);
+      double lon = atan2(n.y, n.x);
       if (lon < 0.0) lon += kPi2;
       c.cclon[t] = lon;
-      c.cclat[t] = asin(nz);
+      c.cclat[t] = asin(n.z);
     }
-  }
-};
-
-struct KV2T {
-  FM_HD static void run(const VdCtx& c, int t) {
-    I4 v = c.tri[t];
-    FM_ATOMIC_MIN32(&c.v2t[v.x], t);
-    FM_ATOMIC_MIN32(&c.v2t[v.y], t);
-    FM_ATOMIC_MIN32(&c.v2t[v.z], t);
   }
 };
 
@@ -110,7 +93,7 @@ struct KDegree {
     int k, t0 = ring_start(c, i, k), t = t0, d = 0;
     do { t = ring_next(c, t, k); d++; } while (t != t0 && d < 4096);
     if (t != t0) *c.err |= FM_E_TOPOLOGY;
-    c.deg[c.orig[i]] = d;
+    c.deg[(int)c.pts[i].id] = d;
   }
 };
 
@@ -122,23 +105,27 @@ struct KRingFill {
   FM_HD static void run(const VdCtx& c, int i) {
     int k, t0 = ring_start(c, i, k), t = t0, d = 0, best = 0x7fffffff, jbest = 0;
     do {
-      int nb = c.orig[geti(c.tri[t], (k + 2) % 3)];
+      int nb = (int)c.pts[geti(c.tri[t], (k + 2) % 3)].id;
       if (nb < best) { best = nb; jbest = d; }
       t = ring_next(c, t, k);
       d++;
     } while (t != t0 && d < 4096);
-    int off = c.deg[c.orig[i]];
+    int off = c.deg[(int)c.pts[i].id];
     t = ring_start(c, i, k);
     for (int j = 0; j < d; j++) {
       int pos = off + (j - jbest + d) % d;
       c.ring_tri[pos] = t + 1;
-      c.ring_nbr[pos] = c.orig[geti(c.tri[t], (k + 2) % 3)] + 1;
+      c.ring_nbr[pos] = (int)c.pts[geti(c.tri[t], (k + 2) % 3)].id + 1;
       t = ring_next(c, t, k);
     }
   }
 };
 
 // ------------------------------------------------------------------- Lloyd
+// Specification: SURVEY.md 7.3 (the reference has no Lloyd step).  For cell i with generator
+// g and CCW ring of circumcentres c_1..c_d: sub-triangles (g, c_j, c_j+1), planar area A_j,
+// degree-5 seven-point rule with nodes q_k projected to the sphere, moment
+// M = sum_j A_j sum_k w_k rho(q^_k) q^_k, new generator M/|M|.
 FM_HD inline double density_eval(const Density& r, double x, double y, double z) {
   if (r.kind == 0) return 1.0;
   double dot = x * r.cx + y * r.cy + z * r.cz;
@@ -155,55 +142,99 @@ FM_HD inline double density_eval(const Density& r, double x, double y, double z)
 #define FM_QW1 0.12593918054482715260
 #define FM_QW2 0.13239415278850618074
 
-FM_HD inline void quad_node(const Density& r, double w, double l0, double l1, double l2, double g0,
-                            double g1, double g2, double a0, double a1, double a2, double b0,
-                            double b1, double b2, double& s0, double& s1, double& s2) {
-  double q0 = l0 * g0 + l1 * a0 + l2 * b0;
-  double q1 = l0 * g1 + l1 * a1 + l2 * b1;
-  double q2 = l0 * g2 + l1 * a2 + l2 * b2;
-  double rr = sqrt(q0 * q0 + q1 * q1 + q2 * q2);
-  q0 /= rr; q1 /= rr; q2 /= rr;
-  double ww = w * density_eval(r, q0, q1, q2);
+FM_HD inline double fm_rsqrt(double v) {
+#if defined(__CUDA_ARCH__)
+  return rsqrt(v);
+#else
+  return 1.0 / sqrt(v);
+#endif
+}
+
+// One node: direction q (any positive scale), weight w.  Projection by rsqrt: the node
+// only enters through q/|q|, so barycentric combinations are formed up to a common factor
+// (S + kappa * vertex instead of A*S + (B-A)*vertex), 3 FMAs per node.
+template <bool UNIFORM>
+FM_HD inline void quad_node(const Density& r, double w, double q0, double q1, double q2, double& s0,
+                            double& s1, double& s2) {
+  double inv = fm_rsqrt(q0 * q0 + q1 * q1 + q2 * q2);
+  q0 *= inv; q1 *= inv; q2 *= inv;
+  double ww = UNIFORM ? w : w * density_eval(r, q0, q1, q2);
   s0 += ww * q0; s1 += ww * q1; s2 += ww * q2;
 }
 
+template <bool UNIFORM>
+FM_HD inline void quad_subtriangle(const Density& r, const P3& g, const P3& a, const P3& b, double& M0,
+                                   double& M1, double& M2) {
+  const double k1 = (FM_QB1 - FM_QA1) / FM_QA1, k2 = (FM_QB2 - FM_QA2) / FM_QA2;
+  double u0 = a.x - g.x, u1 = a.y - g.y, u2 = a.z - g.z;
+  double v0 = b.x - g.x, v1 = b.y - g.y, v2 = b.z - g.z;
+  double c0 = u1 * v2 - u2 * v1, c1 = u2 * v0 - u0 * v2, c2 = u0 * v1 - u1 * v0;
+  double A = 0.5 * sqrt(c0 * c0 + c1 * c1 + c2 * c2);
+  double S0 = g.x + a.x + b.x, S1 = g.y + a.y + b.y, S2 = g.z + a.z + b.z;
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+  quad_node<UNIFORM>(r, FM_QW0, S0, S1, S2, s0, s1, s2);
+  quad_node<UNIFORM>(r, FM_QW1, S0 + k1 * g.x, S1 + k1 * g.y, S2 + k1 * g.z, s0, s1, s2);
+  quad_node<UNIFORM>(r, FM_QW1, S0 + k1 * a.x, S1 + k1 * a.y, S2 + k1 * a.z, s0, s1, s2);
+  quad_node<UNIFORM>(r, FM_QW1, S0 + k1 * b.x, S1 + k1 * b.y, S2 + k1 * b.z, s0, s1, s2);
+  quad_node<UNIFORM>(r, FM_QW2, S0 + k2 * g.x, S1 + k2 * g.y, S2 + k2 * g.z, s0, s1, s2);
+  quad_node<UNIFORM>(r, FM_QW2, S0 + k2 * a.x, S1 + k2 * a.y, S2 + k2 * a.z, s0, s1, s2);
+  quad_node<UNIFORM>(r, FM_QW2, S0 + k2 * b.x, S1 + k2 * b.y, S2 + k2 * b.z, s0, s1, s2);
+  M0 += A * s0; M1 += A * s1; M2 += A * s2;
+}
+
+static const int kRingCap = 12;  // ring slots staged per cell; longer rings take the re-walk path
+
 struct KCentroid {
-  // returns the chord displacement of cell i and moves its generator
-  FM_HD static double compute(const VdCtx& c, int i) {
-    double g0 = c.x[i], g1 = c.y[i], g2 = c.z[i];
-    int k, t0 = ring_start(c, i, k), t = t0, d = 0;
-    double a0 = c.ccx[t], a1 = c.ccy[t], a2 = c.ccz[t];
-    double M0 = 0.0, M1 = 0.0, M2 = 0.0;
+  // Returns the chord displacement of cell i and moves its generator.  ring[j * stride] is
+  // scratch for kRingCap triangle ids (shared memory on the device).  The accumulation starts
+  // at the LOWEST triangle id of the ring, whatever triangle v2t points at, so the result does
+  // not depend on which incident triangle happens to be remembered.
+  template <bool UNIFORM>
+  FM_HD static double compute(const VdCtx& c, int i, int* ring, int stride) {
+    P4 gq = c.pts[i];
+    P3 g{gq.x, gq.y, gq.z};
+    int k, t0 = ring_start(c, i, k), t = t0, d = 0, jmin = 0, tmin = t0, kmin = k;
     do {
-      int tn = ring_next(c, t, k);
-      double b0 = c.ccx[tn], b1 = c.ccy[tn], b2 = c.ccz[tn];
-      double u0 = a0 - g0, u1 = a1 - g1, u2 = a2 - g2;
-      double v0 = b0 - g0, v1 = b1 - g1, v2 = b2 - g2;
-      double c0 = u1 * v2 - u2 * v1, c1 = u2 * v0 - u0 * v2, c2 = u0 * v1 - u1 * v0;
-      double A = 0.5 * sqrt(c0 * c0 + c1 * c1 + c2 * c2);
-      double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-      const double third = 1.0 / 3.0;
-      quad_node(c.rho, FM_QW0, third, third, third, g0, g1, g2, a0, a1, a2, b0, b1, b2, s0, s1, s2);
-      quad_node(c.rho, FM_QW1, FM_QB1, FM_QA1, FM_QA1, g0, g1, g2, a0, a1, a2, b0, b1, b2, s0, s1, s2);
-      quad_node(c.rho, FM_QW1, FM_QA1, FM_QB1, FM_QA1, g0, g1, g2, a0, a1, a2, b0, b1, b2, s0, s1, s2);
-      quad_node(c.rho, FM_QW1, FM_QA1, FM_QA1, FM_QB1, g0, g1, g2, a0, a1, a2, b0, b1, b2, s0, s1, s2);
-      quad_node(c.rho, FM_QW2, FM_QB2, FM_QA2, FM_QA2, g0, g1, g2, a0, a1, a2, b0, b1, b2, s0, s1, s2);
-      quad_node(c.rho, FM_QW2, FM_QA2, FM_QB2, FM_QA2, g0, g1, g2, a0, a1, a2, b0, b1, b2, s0, s1, s2);
-      quad_node(c.rho, FM_QW2, FM_QA2, FM_QA2, FM_QB2, g0, g1, g2, a0, a1, a2, b0, b1, b2, s0, s1, s2);
-      M0 += A * s0; M1 += A * s1; M2 += A * s2;
-      a0 = b0; a1 = b1; a2 = b2;
-      t = tn;
+      if (d < kRingCap) ring[d * stride] = t;
+      if (t < tmin) { tmin = t; jmin = d; kmin = k; }
+      t = ring_next(c, t, k);
       d++;
     } while (t != t0 && d < 4096);
+    if (t != t0) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
+    double M0 = 0.0, M1 = 0.0, M2 = 0.0;
+    if (d <= kRingCap) {
+      int j = jmin;
+      P4 qa = c.cc[tmin];
+      j = (j + 1 == d) ? 0 : j + 1;
+      P4 qb = c.cc[ring[j * stride]];
+      for (int s = 0; s < d; s++) {
+        j = (j + 1 == d) ? 0 : j + 1;
+        P4 qn = c.cc[ring[j * stride]];  // prefetch: consumed in the next iteration
+        quad_subtriangle<UNIFORM>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, M0, M1, M2);
+        qa = qb;
+        qb = qn;
+      }
+    } else {  // long ring: walk again from the lowest triangle
+      t = tmin; k = kmin;
+      P4 qa = c.cc[t];
+      for (int s = 0; s < d; s++) {
+        t = ring_next(c, t, k);
+        P4 qb = c.cc[t];
+        quad_subtriangle<UNIFORM>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, M0, M1, M2);
+        qa = qb;
+      }
+    }
     double nrm = sqrt(M0 * M0 + M1 * M1 + M2 * M2);
-    if (!(nrm > 0.0) || t != t0) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
+    if (!(nrm > 0.0)) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
     double n0 = M0 / nrm, n1 = M1 / nrm, n2 = M2 / nrm;
-    double dx = n0 - g0, dy = n1 - g1, dz = n2 - g2;
-    c.x[i] = n0; c.y[i] = n1; c.z[i] = n2;
+    double dx = n0 - g.x, dy = n1 - g.y, dz = n2 - g.z;
+    c.pts[i].x = n0; c.pts[i].y = n1; c.pts[i].z = n2;
     return sqrt(dx * dx + dy * dy + dz * dz);
   }
   FM_HD static void run(const VdCtx& c, int j) {  // generic form (host tests)
-    double disp = compute(c, c.cell_begin + j);
+    int ring[kRingCap];
+    double disp = (c.rho.kind == 0) ? compute<true>(c, c.cell_begin + j, ring, 1)
+                                    : compute<false>(c, c.cell_begin + j, ring, 1);
     FM_ATOMIC_MAX64(c.maxdisp, dbits(disp));
   }
 };

@@ -184,12 +184,11 @@ class Mesh:
         return md.value
 
     def generator_block(self):
-        """Device pointers and block bounds for the generator all-gather."""
-        px, py, pz = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        """(device pointer, n_padded, begin, count) of the 32-byte generator records."""
+        p = C.c_void_p()
         npad, beg, cnt = C.c_int64(), C.c_int64(), C.c_int64()
-        self._chk(_lib.lib().fm_generator_block(self._h, C.byref(px), C.byref(py), C.byref(pz),
-                                                C.byref(npad), C.byref(beg), C.byref(cnt)))
-        return (px.value, py.value, pz.value), npad.value, beg.value, cnt.value
+        self._chk(_lib.lib().fm_generator_block(self._h, C.byref(p), C.byref(npad), C.byref(beg), C.byref(cnt)))
+        return p.value, npad.value, beg.value, cnt.value
 
     # ---- measurement
     def timer_begin(self):

@@ -135,11 +135,11 @@ module fishman_gpu_c
       real(c_double), intent(out) :: max_disp
     end function fm_lloyd_local
 
-    integer(c_int) function fm_generator_block(h, dx, dy, dz, n_padded, begin, count) &
+    integer(c_int) function fm_generator_block(h, d_records, n_padded, begin, count) &
         bind(C, name='fm_generator_block')
       import :: c_int, c_int64_t, c_ptr
       type(c_ptr), value :: h
-      type(c_ptr), intent(out) :: dx, dy, dz
+      type(c_ptr), intent(out) :: d_records
       integer(c_int64_t), intent(out) :: n_padded, begin, count
     end function fm_generator_block
 

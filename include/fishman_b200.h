@@ -93,10 +93,11 @@ int fm_lloyd(fm_handle* h, const fm_density* rho, int32_t max_iter, double tol, 
  * then all-gathers the blocks in place (fm_generator_block gives the device pointers) and
  * the next call sees the full set.  *max_disp is the rank-local maximum. */
 int fm_lloyd_local(fm_handle* h, const fm_density* rho, int32_t warm, double* max_disp);
-/* Device layout for the generator exchange: three arrays of n_padded doubles (x, y, z in
- * internal order); the rank's block is [begin, begin + count). */
-int fm_generator_block(fm_handle* h, void** dx, void** dy, void** dz, int64_t* n_padded,
-                       int64_t* begin, int64_t* count);
+/* Device layout for the generator exchange: one array of n_padded 32-byte records
+ * { double x, y, z; int64 original_id } in internal (space-filling-curve) order; the rank's
+ * block is records [begin, begin + count).  One in-place all-gather of count records per rank
+ * completes an iteration. */
+int fm_generator_block(fm_handle* h, void** d_records, int64_t* n_padded, int64_t* begin, int64_t* count);
 /* generators in input order (device -> host) */
 int fm_get_generators(fm_handle* h, double* x, double* y, double* z);
 /* replace the generators (host -> device), keeping the internal order and topology */

@@ -31,15 +31,22 @@ struct HostBackend {
     int best = 0;
     double bv = -1e300;
     for (int i = 0; i < c.n; i++) {
-      double v = c.x[i] * d[0] + c.y[i] * d[1] + c.z[i] * d[2];
+      double v = c.pts[i].x * d[0] + c.pts[i].y * d[1] + c.pts[i].z * d[2];
       if (v > bv) { bv = v; best = i; }
     }
     return best;
   }
   P3 fetch_point(const DtCtx& c, int i) { return ldp(c, i); }
-  int fetch_orig(const DtCtx& c, int i) { return c.orig[i]; }
+  int fetch_orig(const DtCtx& c, int i) { return (int)c.pts[i].id; }
   void write_tris(const DtCtx& c, int t0, int cnt, const I4* tri, const I4* adj) {
-    for (int i = 0; i < cnt; i++) { c.tri[t0 + i] = tri[i]; c.adj[t0 + i] = adj[i]; }
+    for (int i = 0; i < cnt; i++) {
+      c.tri[t0 + i] = tri[i]; c.adj[t0 + i] = adj[i];
+      c.v2t[tri[i].x] = c.v2t[tri[i].y] = c.v2t[tri[i].z] = t0 + i;
+    }
+  }
+  int flip_loop(DtCtx& c, int* list[2], int cur, bool skip_check, int* stamp, DtStats* st, char* msg,
+                size_t msglen, int) {
+    return dt_flip_loop_host(*this, c, list, cur, skip_check, stamp, st, msg, msglen);
   }
 };
 
@@ -60,16 +67,16 @@ extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_
     for (int i = 0; i < n; i++) key[i] = morton_key(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
     std::stable_sort(orig.begin(), orig.end(), [&](int a, int b) { return key[a] < key[b]; });
   }
-  std::vector<double> x(n), y(n), z(n);
-  for (int i = 0; i < n; i++) { x[i] = xyz[3 * orig[i]]; y[i] = xyz[3 * orig[i] + 1]; z[i] = xyz[3 * orig[i] + 2]; }
+  std::vector<P4> pts(n);
+  for (int i = 0; i < n; i++) pts[i] = P4{xyz[3 * orig[i]], xyz[3 * orig[i] + 1], xyz[3 * orig[i] + 2], orig[i]};
   int T = 2 * n - 4;
   std::vector<I4> tri(T), adj(T);
-  std::vector<int> loc(n, 0), rank(T), flip_edge(T), role(T, 0), amark(T, 0), listA(T), listB(T);
+  std::vector<int> loc(n, 0), rank(T + 1), flip_edge(T), role(T, 0), amark(T, 0), listA(T), listB(T), v2t(n, -1);
   std::vector<u64> winner(T), vote(T, kNone64), mailbox(3 * (size_t)T, 0);
-  int counters[4] = {0, 0, 0, 0}, err = 0;
+  int counters[8] = {0, 0, 0, 0, 0, 0, 0, 0}, err = 0;
   DtCtx c;
   memset(&c, 0, sizeof c);
-  c.n = n; c.x = x.data(); c.y = y.data(); c.z = z.data(); c.orig = orig.data();
+  c.n = n; c.pts = pts.data(); c.v2t = v2t.data();
   c.tri = tri.data(); c.adj = adj.data(); c.loc = loc.data(); c.winner = winner.data();
   c.rank = rank.data(); c.vote = vote.data(); c.flip_edge = flip_edge.data(); c.role = role.data();
   c.mailbox = mailbox.data(); c.amark = amark.data(); c.counters = counters; c.err = &err;
