@@ -26,7 +26,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB
+    path = os.environ.get("FM_LIB", _build.LIB)  # FM_LIB: an alternative build of the same library (tuning runs)
     if not os.path.exists(path):
         raise RuntimeError(f"{path} is missing: run `python -m fishman_b200.build` (needs nvcc); "
                            "fishman_b200 has no CPU fallback")

@@ -249,7 +249,7 @@ struct KCheck {
     int fe = -1;
     for (int k = 0; k < 3; k++) {
       int ne = geti(a, k), n = ne >> 2, e = ne & 3;
-      int d = geti(c.tri[n], e);
+      int d = ((const int*)c.tri)[4 * (size_t)n + e];
       P3 pd = ldv(c, d, idd);
       if (incircle(pa, pb, pc, pd, ia, ib, ic, idd) > 0) { fe = k; break; }
     }
@@ -272,17 +272,26 @@ struct KSweep {
   FM_HD static void run(const DtCtx& c, int t) {
     I4 v = c.tri[t];
     I4 a = c.adj[t];
-    int ia, ib, ic, idd;
-    P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
+    // stage 1: everything that depends only on the two rows -- three vertex records and the
+    // three opposite-vertex ids -- is requested before anything is consumed
+    P4 qa = c.pts[v.x], qb = c.pts[v.y], qc = c.pts[v.z];
+    const int* trow = (const int*)c.tri;
+    int n0 = a.x >> 2, n1 = a.y >> 2, n2 = a.z >> 2;
+    int d0 = n0 > t ? trow[4 * (size_t)n0 + (a.x & 3)] : -1;
+    int d1 = n1 > t ? trow[4 * (size_t)n1 + (a.y & 3)] : -1;
+    int d2 = n2 > t ? trow[4 * (size_t)n2 + (a.z & 3)] : -1;
+    // stage 2: the opposite vertices
+    P4 z = {0, 0, 0, 0};
+    P4 q0 = d0 >= 0 ? c.pts[d0] : z;
+    P4 q1 = d1 >= 0 ? c.pts[d1] : z;
+    P4 q2 = d2 >= 0 ? c.pts[d2] : z;
+    P3 pa{qa.x, qa.y, qa.z}, pb{qb.x, qb.y, qb.z}, pc{qc.x, qc.y, qc.z};
+    int ia = (int)qa.id, ib = (int)qb.id, ic = (int)qc.id;
     if (orient(pa, pb, pc, ia, ib, ic) <= 0) FM_ATOMIC_ADD32(&c.counters[3], 1);
     int fe = -1;
-    for (int k = 0; k < 3; k++) {
-      int ne = geti(a, k), n = ne >> 2, e = ne & 3;
-      if (n < t) continue;
-      int d = geti(c.tri[n], e);
-      P3 pd = ldv(c, d, idd);
-      if (incircle(pa, pb, pc, pd, ia, ib, ic, idd) > 0) { fe = k; break; }
-    }
+    if (d0 >= 0 && incircle(pa, pb, pc, P3{q0.x, q0.y, q0.z}, ia, ib, ic, (int)q0.id) > 0) fe = 0;
+    else if (d1 >= 0 && incircle(pa, pb, pc, P3{q1.x, q1.y, q1.z}, ia, ib, ic, (int)q1.id) > 0) fe = 1;
+    else if (d2 >= 0 && incircle(pa, pb, pc, P3{q2.x, q2.y, q2.z}, ia, ib, ic, (int)q2.id) > 0) fe = 2;
     if (fe >= 0) {
       c.flip_edge[t] = fe;
       u64 key = vote_key(c.stamp, t);

@@ -16,9 +16,20 @@ __device__ __forceinline__ void use_device_stamp(DtCtx& c) {
 }
 __device__ __forceinline__ void use_device_stamp(VdCtx&) {}
 
+// Resident 256-thread blocks per SM the launcher asks ptxas to make room for.  The gather
+// kernels are latency bound: their exact-arithmetic slow paths are out of line, so the fast
+// paths fit 64-80 registers and the extra resident warps hide the gather latency.
+template <class K> struct KOcc { static const int value = 1; };
+#ifndef FM_OCC_SWEEP
+#define FM_OCC_SWEEP 4
+#endif
+template <> struct KOcc<KSweep> { static const int value = FM_OCC_SWEEP; };
+template <> struct KOcc<KLocateVote> { static const int value = 3; };
+template <> struct KOcc<KCheck> { static const int value = 3; };
+
 // Generic launcher: one thread per work item running a body from *_kernels.cuh.
 template <class K, class Ctx>
-__global__ void __launch_bounds__(256) fm_kernel(Ctx c, int n) {
+__global__ void __launch_bounds__(256, KOcc<K>::value) fm_kernel(Ctx c, int n) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   use_device_stamp(c);
   if (i < n) K::run(c, i);

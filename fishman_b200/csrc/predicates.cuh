@@ -249,6 +249,14 @@ FM_HD inline int orient_slow(P3 a, P3 b, P3 c, int ia, int ib, int ic) {
 // below; 1e-15 ~ 9 u keeps the same margin.
 #define FM_INCIRCLE_ERR 1.0e-15
 
+// stage 1 alone: +1 / -1 when the filter certifies the sign, 0 when it cannot (the caller
+// hands the item to a kernel that runs the full predicate)
+FM_HD inline int orient_fast(const P3& a, const P3& b, const P3& c) {
+  double perm, det = orient_det(a, b, c, perm);
+  double bound = FM_ORIENT_ERR * perm;
+  return det > bound ? 1 : (-det > bound ? -1 : 0);
+}
+
 FM_HD inline int orient(const P3& a, const P3& b, const P3& c, int ia, int ib, int ic) {
   double perm, det = orient_det(a, b, c, perm);
   double bound = FM_ORIENT_ERR * perm;
@@ -290,6 +298,12 @@ FM_HD inline int incircle_slow(P3 a, P3 b, P3 c, P3 d, int ia, int ib, int ic, i
   int s = exact_det_sign(M, 4);
   if (s == 0) s = sos_sign(M, 4);
   return -s * par;  // det4[(a 1);(b 1);(c 1);(d 1)] = det3[a-d; b-d; c-d]
+}
+
+FM_HD inline int incircle_fast(const P3& a, const P3& b, const P3& c, const P3& d) {
+  double perm, det = incircle_det(a, b, c, d, perm);
+  double bound = FM_INCIRCLE_ERR * perm;
+  return det > bound ? 1 : (-det > bound ? -1 : 0);
 }
 
 FM_HD inline int incircle(const P3& a, const P3& b, const P3& c, const P3& d, int ia, int ib,

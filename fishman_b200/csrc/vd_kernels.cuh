@@ -142,9 +142,18 @@ FM_HD inline double density_eval(const Density& r, double x, double y, double z)
 #define FM_QW1 0.12593918054482715260
 #define FM_QW2 0.13239415278850618074
 
+// 1/sqrt(v) for v of order 1: hardware seed (MUFU.RSQ64H, ~2^-22) + two Newton steps in
+// fp64 = 7 DFMA-class instructions instead of the ~20 of the library call; relative error
+// ~2e-16 after the second step (1.5 e^2 per step).
 FM_HD inline double fm_rsqrt(double v) {
 #if defined(__CUDA_ARCH__)
-  return rsqrt(v);
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
+  double hv = 0.5 * v;
+  double e = fma(-hv * y, y, 0.5);
+  y = fma(y, e, y);
+  e = fma(-hv * y, y, 0.5);
+  return fma(y, e, y);
 #else
   return 1.0 / sqrt(v);
 #endif
@@ -157,9 +166,14 @@ template <bool UNIFORM>
 FM_HD inline void quad_node(const Density& r, double w, double q0, double q1, double q2, double& s0,
                             double& s1, double& s2) {
   double inv = fm_rsqrt(q0 * q0 + q1 * q1 + q2 * q2);
-  q0 *= inv; q1 *= inv; q2 *= inv;
-  double ww = UNIFORM ? w : w * density_eval(r, q0, q1, q2);
-  s0 += ww * q0; s1 += ww * q1; s2 += ww * q2;
+  if (UNIFORM) {
+    double ww = w * inv;
+    s0 += ww * q0; s1 += ww * q1; s2 += ww * q2;
+  } else {
+    q0 *= inv; q1 *= inv; q2 *= inv;
+    double ww = w * density_eval(r, q0, q1, q2);
+    s0 += ww * q0; s1 += ww * q1; s2 += ww * q2;
+  }
 }
 
 template <bool UNIFORM>
