@@ -3,6 +3,8 @@
 // CPU logic tests (tests/emu) run the SAME round structure:
 //
 //   Backend::launch<K>(ctx, n)            run body K for thread ids [0, n)
+//   Backend::launch_filtered<K>(ctx, n)   K<false> (fp64 filters only) for [0, n), then K<true>
+//                                         (exact) for the items K<false> deferred
 //   Backend::fill64(ptr, value, count)    device memset of 64-bit words
 //   Backend::fill32(ptr, value, count)
 //   Backend::exclusive_scan(ptr, n)       in place over ints; returns the total
@@ -174,7 +176,7 @@ int dt_flip_loop_host(B& be, DtCtx& c, int* list[2], int cur, bool skip_check, i
     c.n_active = nact;
     c.next_active = list[cur ^ 1];
     c.qcount = c.counters + (cur ^ 1);
-    if (!skip_check) be.template launch<KCheck>(c, nact);
+    if (!skip_check) be.template launch_filtered<KCheckT>(c, nact);
     skip_check = false;
     be.template launch<KMark>(c, nact);
     be.template launch<KFlip>(c, nact);
@@ -201,13 +203,14 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, cha
   int remaining = c.n - 4;
   c.n_tri = 4;
   memset(st, 0, sizeof *st);
-  int zero[8] = {0, 0, 0, 0, 0, 0, 0, 0}, host[8];
+  int zero[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, host[8];
   int* list[2] = {listA, listB};
   be.write_ints(c.counters, zero, 7);
+  be.write_ints(c.counters + 8, zero, 1);
   while (remaining > 0) {
     st->rounds++;
     be.fill64(c.winner, kNone64, (size_t)c.n_tri);
-    be.template launch<KLocateVote>(c, c.n);
+    be.template launch_filtered<KLocateVoteT>(c, c.n);
     be.template launch<KSplitFlag>(c, c.n_tri);
     int nsplit = be.exclusive_scan(c.rank, c.n_tri);
     be.read_ints(host, c.err, 1);
@@ -239,14 +242,15 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, cha
 template <class B>
 int dt_repair_async(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, char* msg,
                     size_t msglen) {
-  int zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int zero[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
   int* list[2] = {listA, listB};
   memset(st, 0, sizeof *st);
   be.write_ints(c.counters, zero, 7);
+  be.write_ints(c.counters + 8, zero, 1);
   c.stamp = *stamp;
   c.next_active = list[0];
   c.qcount = c.counters;
-  be.template launch<KSweep>(c, c.n_tri);
+  be.template launch_filtered<KSweepT>(c, c.n_tri);
   return be.flip_loop(c, list, 0, true, stamp, st, msg, msglen, -1);
 }
 

@@ -87,8 +87,25 @@ struct DtCtx {
   int* counters;               // [0],[1] queue lengths (ping-pong), [2] flips, [3] turned-over
                                // triangles, [4] splits, [5] flip sub-rounds, [6] largest queue,
                                // [7] next unused stamp (device-resident copy)
+  int* slow;                   // items whose fp64 filter was inconclusive (length in counters[8]);
+                               // a second launch runs the exact predicates on them
   int* err;
 };
+
+// Filtered-then-exact, kernel level.  K<false> bodies evaluate only the fp64 filters (no
+// calls, no stack frame, half the registers); an item with an inconclusive filter is pushed
+// here and redone from scratch by K<true>, whose predicates go on to expansion arithmetic
+// and the SoS tie-break.  K<true> alone is always correct (CPU logic tests, cooperative loop).
+FM_HD inline void defer_item(const DtCtx& c, int item);
+
+template <bool EXACT>
+FM_HD inline int orient_t(const P3& a, const P3& b, const P3& cc, int ia, int ib, int ic) {
+  return EXACT ? orient(a, b, cc, ia, ib, ic) : orient_fast(a, b, cc);
+}
+template <bool EXACT>
+FM_HD inline int incircle_t(const P3& a, const P3& b, const P3& cc, const P3& d, int ia, int ib, int ic, int idd) {
+  return EXACT ? incircle(a, b, cc, d, ia, ib, ic, idd) : incircle_fast(a, b, cc, d);
+}
 
 FM_HD inline P3 ldp(const DtCtx& c, int i) { const P4& q = c.pts[i]; return P3{q.x, q.y, q.z}; }
 // point and SoS id with two 16-byte loads of the same sector
@@ -138,6 +155,11 @@ FM_HD inline u64 morton_key(double x, double y, double z) {
   return spread21((u64)fx) | (spread21((u64)fy) << 1) | (spread21((u64)fz) << 2);
 }
 
+FM_HD inline void defer_item(const DtCtx& c, int item) {
+  int pos = FM_ATOMIC_ADD32(&c.counters[8], 1);
+  c.slow[pos] = item;
+}
+
 FM_HD inline void queue_active(const DtCtx& c, int t, int stamp) {
   if (FM_ATOMIC_EXCH32(&c.amark[t], stamp) != stamp) {
     int pos = FM_ATOMIC_ADD32(c.qcount, 1);
@@ -150,7 +172,8 @@ FM_HD inline void queue_active(const DtCtx& c, int t, int stamp) {
 // DV:303-317: a visibility walk from the remembered slot to the triangle that
 // contains the point (three orient tests per step, the edge just crossed is
 // not re-tested), then a vote for that triangle.
-struct KLocateVote {
+template <bool EXACT>
+struct KLocateVoteT {
   FM_HD static void run(const DtCtx& c, int p) {
     int t = c.loc[p];
     if (t < 0) return;
@@ -162,11 +185,16 @@ struct KLocateVote {
       I4 a = c.adj[t];
       int ia, ib, ic;
       P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
-      int next = -1;
+      int next = -1, s = 1;
       // edge opposite vertex k is (v[k+1], v[k+2]); q must be on its left
-      if ((a.x >> 2) != from && orient(pb, pc, q, ib, ic, qi) < 0) next = a.x >> 2;
-      else if ((a.y >> 2) != from && orient(pc, pa, q, ic, ia, qi) < 0) next = a.y >> 2;
-      else if ((a.z >> 2) != from && orient(pa, pb, q, ia, ib, qi) < 0) next = a.z >> 2;
+      if ((a.x >> 2) != from && (s = orient_t<EXACT>(pb, pc, q, ib, ic, qi)) <= 0) next = a.x >> 2;
+      else if ((a.y >> 2) != from && (s = orient_t<EXACT>(pc, pa, q, ic, ia, qi)) <= 0) next = a.y >> 2;
+      else if ((a.z >> 2) != from && (s = orient_t<EXACT>(pa, pb, q, ia, ib, qi)) <= 0) next = a.z >> 2;
+      if (!EXACT && s == 0) {  // inconclusive: the exact kernel resumes the walk from here
+        c.loc[p] = t;
+        defer_item(c, p);
+        return;
+      }
       if (next < 0) break;
       from = t;
       t = next;
@@ -177,6 +205,7 @@ struct KLocateVote {
     FM_ATOMIC_MIN64(&c.winner[t], key);
   }
 };
+typedef KLocateVoteT<true> KLocateVote;
 
 // One thread per triangle: 1 if it splits this round (input of the scan).
 struct KSplitFlag {
@@ -239,7 +268,8 @@ FM_HD inline u64 vote_key(int stamp, int t) {
   return ((u64)(0x7fffffffu - (unsigned)stamp) << 32) | (unsigned)t;
 }
 
-struct KCheck {
+template <bool EXACT>
+struct KCheckT {
   FM_HD static void run(const DtCtx& c, int i) {
     int t = c.active[i];
     I4 v = c.tri[t];
@@ -251,7 +281,9 @@ struct KCheck {
       int ne = geti(a, k), n = ne >> 2, e = ne & 3;
       int d = ((const int*)c.tri)[4 * (size_t)n + e];
       P3 pd = ldv(c, d, idd);
-      if (incircle(pa, pb, pc, pd, ia, ib, ic, idd) > 0) { fe = k; break; }
+      int s = incircle_t<EXACT>(pa, pb, pc, pd, ia, ib, ic, idd);
+      if (!EXACT && s == 0) { defer_item(c, i); return; }
+      if (s > 0) { fe = k; break; }
     }
     c.flip_edge[t] = fe;
     if (fe >= 0) {
@@ -261,6 +293,7 @@ struct KCheck {
     }
   }
 };
+typedef KCheckT<true> KCheck;
 
 // Warm restart, first sub-round: ONE pass over all triangles that (a) counts triangles that
 // turned over when the generators moved (counters[3]; any -> the caller rebuilds), (b) tests
@@ -268,7 +301,8 @@ struct KCheck {
 // KCheck does, queueing the claimant for the mark/flip/patch phases, and (c) refreshes the
 // circumcentre of every triangle (flips refresh theirs).  Replaces validate + queue_all +
 // flip_check over T + circumcentre: the three vertices are gathered once.
-struct KSweep {
+template <bool EXACT>
+struct KSweepT {
   FM_HD static void run(const DtCtx& c, int t) {
     I4 v = c.tri[t];
     I4 a = c.adj[t];
@@ -287,11 +321,26 @@ struct KSweep {
     P4 q2 = d2 >= 0 ? c.pts[d2] : z;
     P3 pa{qa.x, qa.y, qa.z}, pb{qb.x, qb.y, qb.z}, pc{qc.x, qc.y, qc.z};
     int ia = (int)qa.id, ib = (int)qb.id, ic = (int)qc.id;
-    if (orient(pa, pb, pc, ia, ib, ic) <= 0) FM_ATOMIC_ADD32(&c.counters[3], 1);
-    int fe = -1;
-    if (d0 >= 0 && incircle(pa, pb, pc, P3{q0.x, q0.y, q0.z}, ia, ib, ic, (int)q0.id) > 0) fe = 0;
-    else if (d1 >= 0 && incircle(pa, pb, pc, P3{q1.x, q1.y, q1.z}, ia, ib, ic, (int)q1.id) > 0) fe = 1;
-    else if (d2 >= 0 && incircle(pa, pb, pc, P3{q2.x, q2.y, q2.z}, ia, ib, ic, (int)q2.id) > 0) fe = 2;
+    int so = orient_t<EXACT>(pa, pb, pc, ia, ib, ic);
+    int fe = -1, s = -1;
+    bool unsure = !EXACT && so == 0;
+    if (!unsure && d0 >= 0) {
+      s = incircle_t<EXACT>(pa, pb, pc, P3{q0.x, q0.y, q0.z}, ia, ib, ic, (int)q0.id);
+      if (s > 0) fe = 0;
+      unsure = !EXACT && s == 0;
+    }
+    if (!unsure && fe < 0 && d1 >= 0) {
+      s = incircle_t<EXACT>(pa, pb, pc, P3{q1.x, q1.y, q1.z}, ia, ib, ic, (int)q1.id);
+      if (s > 0) fe = 1;
+      unsure = !EXACT && s == 0;
+    }
+    if (!unsure && fe < 0 && d2 >= 0) {
+      s = incircle_t<EXACT>(pa, pb, pc, P3{q2.x, q2.y, q2.z}, ia, ib, ic, (int)q2.id);
+      if (s > 0) fe = 2;
+      unsure = !EXACT && s == 0;
+    }
+    if (unsure) { defer_item(c, t); return; }
+    if (so < 0) FM_ATOMIC_ADD32(&c.counters[3], 1);
     if (fe >= 0) {
       c.flip_edge[t] = fe;
       u64 key = vote_key(c.stamp, t);
@@ -307,6 +356,7 @@ struct KSweep {
     }
   }
 };
+typedef KSweepT<true> KSweep;
 
 struct KMark {
   FM_HD static void run(const DtCtx& c, int i) {

@@ -27,14 +27,17 @@ static char g_create_err[512];
 // ------------------------------------------------------------------- handle
 template <class K> struct KName { static const char* get() { return "kernel"; } };
 #define FM_KNAME(K, s) template <> struct KName<K> { static const char* get() { return s; } };
-FM_KNAME(KLocateVote, "locate_vote")
+FM_KNAME(KLocateVote, "locate_exact")
+FM_KNAME(KLocateVoteT<false>, "locate_vote")
 FM_KNAME(KSplitFlag, "split_flag")
 FM_KNAME(KSplit, "split13")
-FM_KNAME(KCheck, "flip_check")
+FM_KNAME(KCheck, "check_exact")
+FM_KNAME(KCheckT<false>, "flip_check")
 FM_KNAME(KMark, "flip_mark")
 FM_KNAME(KFlip, "flip22")
 FM_KNAME(KPatch, "flip_patch")
-FM_KNAME(KSweep, "sweep")
+FM_KNAME(KSweep, "sweep_exact")
+FM_KNAME(KSweepT<false>, "sweep")
 FM_KNAME(KValidate, "validate")
 FM_KNAME(KCircum, "circumcentre")
 FM_KNAME(KDegree, "ring_degree")
@@ -68,7 +71,7 @@ struct fm_handle {
   size_t cub_bytes = 0;
   int* pinned = nullptr;
   int stamp = 1;  // host mirror (unused by the device-resident flip loop)
-  int coop_blocks = 0;
+  int coop_blocks = 0, sms = 0;
   bool have_dt = false, have_cc = false, have_vd = false, have_edges = false;
   // Voronoi
   P4* cc = nullptr;
@@ -158,7 +161,7 @@ struct fm_handle {
     c.n = n; c.pts = pts; c.v2t = v2t; c.tri = tri; c.adj = adj; c.loc = loc;
     c.winner = winner; c.rank = rankbuf; c.n_tri = n_tri; c.stamp = stamp; c.stamp_dev = counters + 7;
     c.vote = vote; c.flip_edge = flip_edge; c.role = role; c.mailbox = mailbox; c.amark = amark;
-    c.counters = counters; c.qcount = counters; c.err = err;
+    c.counters = counters; c.qcount = counters; c.err = err; c.slow = rankbuf;
     return c;
   }
   VdCtx vd_ctx(const Density* rho) {
@@ -178,6 +181,17 @@ struct CudaBackend {
   fm_handle* h;
   template <class K>
   void launch(const DtCtx& c, int n) { h->launch<K, DtCtx>(c, n); }
+  // filter-only kernel over [0, n), then the exact kernel over what it deferred
+  template <template <bool> class K>
+  void launch_filtered(const DtCtx& c, int n) {
+    if (n <= 0) return;
+    h->launch<K<false>, DtCtx>(c, n);
+    h->prof_begin();
+    fm_kernel_deferred<K<true>><<<h->sms * 4, 128, 0, h->stream>>>(c);
+    h->note_cuda(cudaGetLastError(), KName<K<true>>::get());
+    h->prof_end(KName<K<true>>::get(), 0);
+    h->note_cuda(cudaMemsetAsync(c.counters + 8, 0, sizeof(int), h->stream), "deferred reset");
+  }
   void fill64(u64* p, u64 v, size_t n) {
     // only all-ones is ever requested: a byte memset does it
     h->note_cuda(cudaMemsetAsync(p, (int)(v & 0xff), n * sizeof(u64), h->stream), "fill64");
@@ -253,7 +267,7 @@ struct CudaBackend {
       c.n_active = nact;
       c.next_active = list[cur ^ 1];
       c.qcount = c.counters + (cur ^ 1);
-      if (!skip_check) launch<KCheck>(c, nact);
+      if (!skip_check) launch_filtered<KCheckT>(c, nact);
       skip_check = false;
       launch<KMark>(c, nact);
       launch<KFlip>(c, nact);
@@ -313,6 +327,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   A(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fm_flip_coop, 256, 0));
   h->coop_blocks = sms * (per_sm > 0 ? per_sm : 1);
+  h->sms = sms;
   A(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   A(cudaEventCreate(&h->ev0)); A(cudaEventCreate(&h->ev1));
   A(cudaMallocHost((void**)&h->pinned, 64 * sizeof(int)));
@@ -321,7 +336,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(dalloc(&h->tri, T)); A(dalloc(&h->adj, T)); A(dalloc(&h->cc, T));
   A(dalloc(&h->loc, n)); A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T));
-  A(dalloc(&h->counters, 8)); A(dalloc(&h->err, 1));
+  A(dalloc(&h->counters, 16)); A(dalloc(&h->err, 1));
   A(dalloc(&h->winner, T)); A(dalloc(&h->vote, T)); A(dalloc(&h->mailbox, 3 * T)); A(dalloc(&h->scratch64, 4));
   A(cudaMemsetAsync(h->vote, 0xff, sizeof(u64) * T, h->stream));
   A(cudaMemsetAsync(h->role, 0, sizeof(int) * T, h->stream));
@@ -329,7 +344,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(cudaMemsetAsync(h->mailbox, 0, sizeof(u64) * 3 * T, h->stream));
   A(cudaMemsetAsync(h->err, 0, sizeof(int), h->stream));
   A(cudaMemsetAsync(h->pts, 0, sizeof(P4) * h->n_pad, h->stream));
-  int init_counters[8] = {0, 0, 0, 0, 0, 0, 0, 1};  // [7]: first stamp
+  int init_counters[16] = {0, 0, 0, 0, 0, 0, 0, 1};  // [7]: first stamp
   A(cudaMemcpyAsync(h->counters, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, h->stream));
   A(cudaStreamSynchronize(h->stream));
   // staging: input order coordinates, keys, sort buffers

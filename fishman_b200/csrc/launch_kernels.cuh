@@ -17,15 +17,12 @@ __device__ __forceinline__ void use_device_stamp(DtCtx& c) {
 __device__ __forceinline__ void use_device_stamp(VdCtx&) {}
 
 // Resident 256-thread blocks per SM the launcher asks ptxas to make room for.  The gather
-// kernels are latency bound: their exact-arithmetic slow paths are out of line, so the fast
-// paths fit 64-80 registers and the extra resident warps hide the gather latency.
+// kernels are latency / L1 bound; their filter-only forms (K<false>) contain no calls and
+// fit 64 registers without spilling, so four blocks hide the gather latency.
 template <class K> struct KOcc { static const int value = 1; };
-#ifndef FM_OCC_SWEEP
-#define FM_OCC_SWEEP 4
-#endif
-template <> struct KOcc<KSweep> { static const int value = FM_OCC_SWEEP; };
-template <> struct KOcc<KLocateVote> { static const int value = 3; };
-template <> struct KOcc<KCheck> { static const int value = 3; };
+template <> struct KOcc<KSweepT<false>> { static const int value = 4; };
+template <> struct KOcc<KLocateVoteT<false>> { static const int value = 4; };
+template <> struct KOcc<KCheckT<false>> { static const int value = 4; };
 
 // Generic launcher: one thread per work item running a body from *_kernels.cuh.
 template <class K, class Ctx>
@@ -33,6 +30,15 @@ __global__ void __launch_bounds__(256, KOcc<K>::value) fm_kernel(Ctx c, int n) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   use_device_stamp(c);
   if (i < n) K::run(c, i);
+}
+
+// Second half of a filtered launch: the exact body over the deferred items (grid-stride;
+// the count is only known on the device).
+template <class K>
+__global__ void __launch_bounds__(128) fm_kernel_deferred(DtCtx c) {
+  use_device_stamp(c);
+  int m = c.counters[8];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) K::run(c, c.slow[i]);
 }
 
 // All flip sub-rounds of one insertion round (or of one warm repair) in ONE cooperative

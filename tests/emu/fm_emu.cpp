@@ -18,6 +18,16 @@ struct HostBackend {
   void launch(const DtCtx& c, int n) {
     for (int i = 0; i < n; i++) K::run(c, i);
   }
+  // both halves of the filtered-then-exact scheme, as on the device
+  template <template <bool> class K>
+  void launch_filtered(const DtCtx& c, int n) {
+    for (int i = 0; i < n; i++) K<false>::run(c, i);
+    int m = c.counters[8];
+    n_deferred += m;
+    for (int i = 0; i < m; i++) K<true>::run(c, c.slow[i]);
+    c.counters[8] = 0;
+  }
+  long long n_deferred = 0;
   void fill64(u64* p, u64 v, size_t n) { std::fill(p, p + n, v); }
   void fill32(int* p, int v, size_t n) { std::fill(p, p + n, v); }
   int exclusive_scan(int* p, int n) {
@@ -73,13 +83,14 @@ extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_
   std::vector<I4> tri(T), adj(T);
   std::vector<int> loc(n, 0), rank(T + 1), flip_edge(T), role(T, 0), amark(T, 0), listA(T), listB(T), v2t(n, -1);
   std::vector<u64> winner(T), vote(T, kNone64), mailbox(3 * (size_t)T, 0);
-  int counters[8] = {0, 0, 0, 0, 0, 0, 0, 0}, err = 0;
+  int counters[16] = {0}, err = 0;
+  std::vector<int> slow(T + 1);
   DtCtx c;
   memset(&c, 0, sizeof c);
   c.n = n; c.pts = pts.data(); c.v2t = v2t.data();
   c.tri = tri.data(); c.adj = adj.data(); c.loc = loc.data(); c.winner = winner.data();
   c.rank = rank.data(); c.vote = vote.data(); c.flip_edge = flip_edge.data(); c.role = role.data();
-  c.mailbox = mailbox.data(); c.amark = amark.data(); c.counters = counters; c.err = &err;
+  c.mailbox = mailbox.data(); c.amark = amark.data(); c.counters = counters; c.err = &err; c.slow = slow.data();
   HostBackend be;
   int boot[4];
   if (dt_bootstrap(be, c, boot, g_err, sizeof g_err)) return 1;
