@@ -42,6 +42,17 @@ ALG_BYTES = {
 }
 
 
+def ncu_traffic(kernel, n):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed
+    ncu --set full capture (profiles/traffic.json), valid for the generator count it was taken at."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return t["kernels"][kernel]["dram_bytes_per_launch"] if t["generators"] == n else None
+    except Exception:
+        return None
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -258,9 +269,13 @@ def run_gpu(args):
         e2e_ms = float(t.item())
 
     # ---- per-kernel times (CUDA events around every launch on the launching stream)
+    # a second pass over the same K steps with a CUDA-event pair around every launch (pairs are
+    # resolved at the points where the host waits anyway: no extra synchronisation)
     m.profile(True)
     m.stats_reset()
+    m.timer_begin()
     device_steps(args.steps)
+    ms_prof = m.timer_end()
     rows = m.profile_rows()
     m.profile(False)
     barrier()
@@ -283,7 +298,8 @@ def run_gpu(args):
             "gpu_launches": st["launches"],
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": top["name"], "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "traffic": None, "peak_kind": peak_kind,
+                         "frac": ach / peak, "traffic": ncu_traffic(top["name"], n), "peak_kind": peak_kind,
+                         "profiled_pass_ms_per_step": ms_prof / args.steps,
                          "alg_bytes_per_item": ALG_BYTES.get(top["name"], 0),
                          "items_per_launch": top["threads"] / max(top["launches"], 1),
                          "avg_launch_ms": dur_ms, "share_of_step": top["ms"] / tot},

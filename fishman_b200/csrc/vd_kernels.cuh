@@ -142,58 +142,66 @@ FM_HD inline double density_eval(const Density& r, double x, double y, double z)
 #define FM_QW1 0.12593918054482715260
 #define FM_QW2 0.13239415278850618074
 
-// 1/sqrt(v) for v of order 1: hardware seed (MUFU.RSQ64H, ~2^-22) + two Newton steps in
-// fp64 = 7 DFMA-class instructions instead of the ~20 of the library call; relative error
-// ~2e-16 after the second step (1.5 e^2 per step).
+// 1/sqrt(v) for v of order 1: hardware seed (MUFU.RSQ64H, ~2^-22) + ONE cubically convergent
+// step  y (1 + e/2 + 3 e^2/8),  e = 1 - v y^2  = 5 DFMA-class instructions instead of the ~20
+// of the library call; the remaining relative error (~0.3 e^3) is far below 2^-53.
 FM_HD inline double fm_rsqrt(double v) {
 #if defined(__CUDA_ARCH__)
   double y;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
-  double hv = 0.5 * v;
-  double e = fma(-hv * y, y, 0.5);
-  y = fma(y, e, y);
-  e = fma(-hv * y, y, 0.5);
-  return fma(y, e, y);
+  double e = fma(-(v * y), y, 1.0);
+  double p = fma(0.375, e, 0.5);
+  return fma(y, p * e, y);
 #else
   return 1.0 / sqrt(v);
 #endif
 }
 
-// One node: direction q (any positive scale), weight w.  Projection by rsqrt: the node
-// only enters through q/|q|, so barycentric combinations are formed up to a common factor
-// (S + kappa * vertex instead of A*S + (B-A)*vertex), 3 FMAs per node.
+// Quadrature of one sub-triangle (g, a, b) added to the moment M.  The seven nodes are
+// S/3 and (A S + (B - A) v) for v in {g, a, b}, (A, B) in {(A1, B1), (A2, B2)}, S = g + a + b.
+// Only q/|q| enters, so each node is taken as q = S + kappa v (kappa = (B - A)/A) and
+//   |q|^2 = S.S + 2 kappa S.v + kappa^2 v.v,      sum_k w_k q_k/|q_k| = cS S + cg g + ca a + cb b
+// with scalar coefficients: the node vectors themselves are only formed when the density has
+// to be evaluated at them.  gg, aa, bb are the squared norms of g, a, b.
 template <bool UNIFORM>
-FM_HD inline void quad_node(const Density& r, double w, double q0, double q1, double q2, double& s0,
-                            double& s1, double& s2) {
-  double inv = fm_rsqrt(q0 * q0 + q1 * q1 + q2 * q2);
-  if (UNIFORM) {
-    double ww = w * inv;
-    s0 += ww * q0; s1 += ww * q1; s2 += ww * q2;
-  } else {
-    q0 *= inv; q1 *= inv; q2 *= inv;
-    double ww = w * density_eval(r, q0, q1, q2);
-    s0 += ww * q0; s1 += ww * q1; s2 += ww * q2;
-  }
-}
-
-template <bool UNIFORM>
-FM_HD inline void quad_subtriangle(const Density& r, const P3& g, const P3& a, const P3& b, double& M0,
-                                   double& M1, double& M2) {
+FM_HD inline void quad_subtriangle(const Density& r, const P3& g, const P3& a, const P3& b, double gg,
+                                   double aa, double bb, double& M0, double& M1, double& M2) {
   const double k1 = (FM_QB1 - FM_QA1) / FM_QA1, k2 = (FM_QB2 - FM_QA2) / FM_QA2;
   double u0 = a.x - g.x, u1 = a.y - g.y, u2 = a.z - g.z;
   double v0 = b.x - g.x, v1 = b.y - g.y, v2 = b.z - g.z;
   double c0 = u1 * v2 - u2 * v1, c1 = u2 * v0 - u0 * v2, c2 = u0 * v1 - u1 * v0;
-  double A = 0.5 * sqrt(c0 * c0 + c1 * c1 + c2 * c2);
+  double n2 = c0 * c0 + c1 * c1 + c2 * c2;
+  double A = n2 > 0.0 ? 0.5 * n2 * fm_rsqrt(n2) : 0.0;  // planar area; coincident circumcentres give 0
   double S0 = g.x + a.x + b.x, S1 = g.y + a.y + b.y, S2 = g.z + a.z + b.z;
-  double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-  quad_node<UNIFORM>(r, FM_QW0, S0, S1, S2, s0, s1, s2);
-  quad_node<UNIFORM>(r, FM_QW1, S0 + k1 * g.x, S1 + k1 * g.y, S2 + k1 * g.z, s0, s1, s2);
-  quad_node<UNIFORM>(r, FM_QW1, S0 + k1 * a.x, S1 + k1 * a.y, S2 + k1 * a.z, s0, s1, s2);
-  quad_node<UNIFORM>(r, FM_QW1, S0 + k1 * b.x, S1 + k1 * b.y, S2 + k1 * b.z, s0, s1, s2);
-  quad_node<UNIFORM>(r, FM_QW2, S0 + k2 * g.x, S1 + k2 * g.y, S2 + k2 * g.z, s0, s1, s2);
-  quad_node<UNIFORM>(r, FM_QW2, S0 + k2 * a.x, S1 + k2 * a.y, S2 + k2 * a.z, s0, s1, s2);
-  quad_node<UNIFORM>(r, FM_QW2, S0 + k2 * b.x, S1 + k2 * b.y, S2 + k2 * b.z, s0, s1, s2);
-  M0 += A * s0; M1 += A * s1; M2 += A * s2;
+  double SS = S0 * S0 + S1 * S1 + S2 * S2;
+  double Sg = S0 * g.x + S1 * g.y + S2 * g.z;
+  double Sa = S0 * a.x + S1 * a.y + S2 * a.z;
+  double Sb = S0 * b.x + S1 * b.y + S2 * b.z;
+  double i0 = fm_rsqrt(SS);
+  double i1g = fm_rsqrt(fma(k1 * k1, gg, fma(2.0 * k1, Sg, SS)));
+  double i1a = fm_rsqrt(fma(k1 * k1, aa, fma(2.0 * k1, Sa, SS)));
+  double i1b = fm_rsqrt(fma(k1 * k1, bb, fma(2.0 * k1, Sb, SS)));
+  double i2g = fm_rsqrt(fma(k2 * k2, gg, fma(2.0 * k2, Sg, SS)));
+  double i2a = fm_rsqrt(fma(k2 * k2, aa, fma(2.0 * k2, Sa, SS)));
+  double i2b = fm_rsqrt(fma(k2 * k2, bb, fma(2.0 * k2, Sb, SS)));
+  double w0 = FM_QW0 * i0;
+  double w1g = FM_QW1 * i1g, w1a = FM_QW1 * i1a, w1b = FM_QW1 * i1b;
+  double w2g = FM_QW2 * i2g, w2a = FM_QW2 * i2a, w2b = FM_QW2 * i2b;
+  if (!UNIFORM) {  // density at the projected nodes q^ = (S + kappa v) / |q|
+    w0 *= density_eval(r, S0 * i0, S1 * i0, S2 * i0);
+    w1g *= density_eval(r, fma(k1, g.x, S0) * i1g, fma(k1, g.y, S1) * i1g, fma(k1, g.z, S2) * i1g);
+    w1a *= density_eval(r, fma(k1, a.x, S0) * i1a, fma(k1, a.y, S1) * i1a, fma(k1, a.z, S2) * i1a);
+    w1b *= density_eval(r, fma(k1, b.x, S0) * i1b, fma(k1, b.y, S1) * i1b, fma(k1, b.z, S2) * i1b);
+    w2g *= density_eval(r, fma(k2, g.x, S0) * i2g, fma(k2, g.y, S1) * i2g, fma(k2, g.z, S2) * i2g);
+    w2a *= density_eval(r, fma(k2, a.x, S0) * i2a, fma(k2, a.y, S1) * i2a, fma(k2, a.z, S2) * i2a);
+    w2b *= density_eval(r, fma(k2, b.x, S0) * i2b, fma(k2, b.y, S1) * i2b, fma(k2, b.z, S2) * i2b);
+  }
+  double cS = w0 + ((w1g + w1a) + w1b) + ((w2g + w2a) + w2b);
+  double cg = fma(k1, w1g, k2 * w2g), ca = fma(k1, w1a, k2 * w2a), cb = fma(k1, w1b, k2 * w2b);
+  double s0 = fma(cb, b.x, fma(ca, a.x, fma(cg, g.x, cS * S0)));
+  double s1 = fma(cb, b.y, fma(ca, a.y, fma(cg, g.y, cS * S1)));
+  double s2 = fma(cb, b.z, fma(ca, a.z, fma(cg, g.z, cS * S2)));
+  M0 = fma(A, s0, M0); M1 = fma(A, s1, M1); M2 = fma(A, s2, M2);
 }
 
 static const int kRingCap = 12;  // ring slots staged per cell; longer rings take the re-walk path
@@ -216,26 +224,33 @@ struct KCentroid {
     } while (t != t0 && d < 4096);
     if (t != t0) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
     double M0 = 0.0, M1 = 0.0, M2 = 0.0;
+    const double gg = g.x * g.x + g.y * g.y + g.z * g.z;
     if (d <= kRingCap) {
       int j = jmin;
       P4 qa = c.cc[tmin];
       j = (j + 1 == d) ? 0 : j + 1;
       P4 qb = c.cc[ring[j * stride]];
+      double aa = qa.x * qa.x + qa.y * qa.y + qa.z * qa.z;
       for (int s = 0; s < d; s++) {
         j = (j + 1 == d) ? 0 : j + 1;
         P4 qn = c.cc[ring[j * stride]];  // prefetch: consumed in the next iteration
-        quad_subtriangle<UNIFORM>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, M0, M1, M2);
+        double bb = qb.x * qb.x + qb.y * qb.y + qb.z * qb.z;
+        quad_subtriangle<UNIFORM>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gg, aa, bb, M0, M1, M2);
         qa = qb;
         qb = qn;
+        aa = bb;
       }
     } else {  // long ring: walk again from the lowest triangle
       t = tmin; k = kmin;
       P4 qa = c.cc[t];
+      double aa = qa.x * qa.x + qa.y * qa.y + qa.z * qa.z;
       for (int s = 0; s < d; s++) {
         t = ring_next(c, t, k);
         P4 qb = c.cc[t];
-        quad_subtriangle<UNIFORM>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, M0, M1, M2);
+        double bb = qb.x * qb.x + qb.y * qb.y + qb.z * qb.z;
+        quad_subtriangle<UNIFORM>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gg, aa, bb, M0, M1, M2);
         qa = qb;
+        aa = bb;
       }
     }
     double nrm = sqrt(M0 * M0 + M1 * M1 + M2 * M2);

@@ -232,3 +232,24 @@ def test_full_size_properties(fb):
     assert np.abs(np.linalg.norm(g, axis=1) - 1).max() < 4e-16
     assert 0 < md < 0.01
     m.close()
+
+
+@pytest.mark.parametrize("name", ["u300", "fib500", "u2000"])
+def test_against_golden_fixtures(fb, name):
+    """Committed fixtures (tests/golden/make_golden.py): Qhull topology; circumcentres and one
+    Lloyd step (uniform and x4 density) evaluated with 50-digit mpmath."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+    m = fb.Mesh.from_xyz(g["xyz"])
+    m.delaunay_triangulation()
+    m.voronoi_diagram()
+    tri, _ = m.triangles()
+    assert np.array_equal(_check.canonical(tri), g["tri"])
+    if "cc" in g:
+        cc, _ = m.circumcentres()
+        assert _check.max_cc_diff(g["tri_ccw"], g["cc"], tri, cc) < 1e-13
+        for rho, key in ((fb.density_uniform(), "lloyd_uniform"), (fb.density_x4(), "lloyd_x4")):
+            m.set_generators(g["xyz"])
+            m.lloyd(rho, max_iter=1, warm=True)
+            assert np.abs(m.generators() - g[key]).max() < 1e-13
+    m.close()
