@@ -202,15 +202,14 @@ def run_gpu(args):
     m = fb.Mesh.from_xyz(p, rank=rank, size=world)
     gather = None
     if world > 1:
+        from fishman_b200 import sharding
         ptr, npad, beg, cnt = m.generator_block()
-        full = torch.as_tensor(_DevPtr(ptr, 4 * npad), device=f"cuda:{local}")  # 32-byte records as 4 doubles
-        mdt = torch.zeros(1, dtype=torch.float64, device=f"cuda:{local}")
+        assert (npad, beg, cnt) == sharding.block_bounds(n, rank, world)[:3]
+        full = sharding.DeviceRecords(ptr, npad, f"cuda:{local}").tensor  # aliases the handle's records
 
         def gather(md):
-            dist.all_gather_into_tensor(full, full[4 * beg:4 * (beg + cnt)])  # in place: one collective per iteration
-            mdt[0] = md
-            dist.all_reduce(mdt, op=dist.ReduceOp.MAX)
-            return float(mdt.item())  # host sync: the next iteration may start
+            sharding.allgather_blocks(dist, full, beg, cnt)  # in place: one collective per iteration
+            return sharding.reduce_max(dist, md, f"cuda:{local}")  # host sync: the next iteration may start
 
     def barrier():
         torch.cuda.synchronize()
