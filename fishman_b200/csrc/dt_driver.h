@@ -14,6 +14,7 @@
 //   Backend::fetch_point(ctx, i)          coordinates of point i on the host
 //   Backend::fetch_orig(ctx, i)
 //   Backend::write_tris(ctx, t0, cnt, tri, adj)
+//   Backend::prev_coarser(ctx, thr, prev) prev[i] = largest j <= i with point_class(j) > thr, or -1
 //   Backend::flip_loop(ctx, list, cur, skip_check, stamp, stats, msg, len, nact_hint)
 //                                         flip sub-rounds until the queue is empty; nact_hint =
 //                                         length of the first queue when the host knows it, else -1
@@ -193,43 +194,69 @@ int dt_flip_loop_host(B& be, DtCtx& c, int* list[2], int cur, bool skip_check, i
   return 0;
 }
 
-// Runs insertion rounds until every point is a vertex.  Preconditions: the four
-// bootstrap faces are in slots 0..3, loc[] is 0 for every point but the
-// bootstrap ones (-1), vote[] is all ones, role/amark/mailbox hold stamps older
-// than *stamp (zero at first use).  listA/listB: two int queues of 2n-4 entries.
+// Number of coarseness classes above the finest one: the coarsest level holds ~<= 256 points.
+inline int dt_level_count(int n) {
+  int K = 0;
+  while (K < 12 && ((long long)256 << (2 * K)) < n) K++;
+  return K;
+}
+
+// Runs insertion rounds, level by level, until every point is a vertex.  Preconditions: the
+// four bootstrap faces are in slots 0..3, loc[] is 0 for every point but the bootstrap ones
+// (-1), vote[] is all ones, role/amark/mailbox hold stamps older than *stamp (zero at first
+// use).  listA/listB: two int queues of 2n-4 entries.  lvl_order: the points sorted by
+// (level, internal index); lvl_off (host, K+2 entries): start of each level in lvl_order,
+// level L = class K-L; prev: scratch of n ints; boot: the four bootstrap points.
 template <class B>
-int dt_run(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, char* msg,
-           size_t msglen) {
-  int remaining = c.n - 4;
+int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const int* lvl_off, int K,
+           int* prev, const int boot[4], int* stamp, DtStats* st, char* msg, size_t msglen) {
   c.n_tri = 4;
   memset(st, 0, sizeof *st);
   int zero[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, host[8];
   int* list[2] = {listA, listB};
   be.write_ints(c.counters, zero, 7);
   be.write_ints(c.counters + 8, zero, 1);
-  while (remaining > 0) {
-    st->rounds++;
-    be.fill64(c.winner, kNone64, (size_t)c.n_tri);
-    be.template launch_filtered<KLocateVoteT>(c, c.n);
-    be.template launch<KSplitFlag>(c, c.n_tri);
-    int nsplit = be.exclusive_scan(c.rank, c.n_tri);
-    be.read_ints(host, c.err, 1);
-    if (host[0]) {
-      snprintf(msg, msglen, "point location failed (error bits %d): duplicate points?", host[0]);
-      return 1;
+  int boot_class[4];
+  for (int k = 0; k < 4; k++) boot_class[k] = point_class(be.fetch_orig(c, boot[k]), K);
+  c.level_max = K;
+  for (int L = 0; L <= K; L++) {
+    int m = lvl_off[L + 1] - lvl_off[L];
+    int remaining = m;
+    for (int k = 0; k < 4; k++) remaining -= (boot_class[k] == K - L);
+    if (remaining <= 0) continue;
+    c.plist = lvl_order + lvl_off[L];
+    c.n_plist = m;
+    c.level_thr = K - L;
+    if (L > 0) {  // start every walk next to an inserted point (level 0 starts at slot 0)
+      be.prev_coarser(c, K - L, prev);
+      c.prev = prev;
+      be.template launch<KLevelInit>(c, m);
     }
-    if (nsplit <= 0) {
-      snprintf(msg, msglen, "no triangle accepted a point although %d remain", remaining);
-      return 1;
+    while (remaining > 0) {
+      st->rounds++;
+      be.fill64(c.winner, kNone64, (size_t)c.n_tri);
+      be.template launch_filtered<KLocateVoteT>(c, m);
+      be.template launch<KSplitFlag>(c, c.n_tri);
+      int nsplit = be.exclusive_scan(c.rank, c.n_tri);
+      be.read_ints(host, c.err, 1);
+      if (host[0]) {
+        snprintf(msg, msglen, "point location failed (error bits %d): duplicate points?", host[0]);
+        return 1;
+      }
+      if (nsplit <= 0) {
+        snprintf(msg, msglen, "no triangle accepted a point although %d remain in level %d", remaining, L);
+        return 1;
+      }
+      c.stamp = *stamp;
+      c.next_active = list[0];
+      c.qcount = c.counters;
+      be.template launch<KSplit>(c, c.n_tri);
+      remaining -= nsplit;
+      c.n_tri += 2 * nsplit;
+      if (be.flip_loop(c, list, 0, false, stamp, st, msg, msglen, 3 * nsplit)) return 1;
     }
-    c.stamp = *stamp;
-    c.next_active = list[0];
-    c.qcount = c.counters;
-    be.template launch<KSplit>(c, c.n_tri);
-    remaining -= nsplit;
-    c.n_tri += 2 * nsplit;
-    if (be.flip_loop(c, list, 0, false, stamp, st, msg, msglen, 3 * nsplit)) return 1;
   }
+  c.plist = nullptr;
   be.read_ints(host, c.counters, 8);
   st->flips = host[2];
   if (host[5]) { st->subrounds = host[5]; st->max_active = host[6]; }

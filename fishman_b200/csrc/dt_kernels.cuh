@@ -68,6 +68,12 @@ struct DtCtx {
   I4* adj;                     // adj[k] = (neighbour << 2 | its edge index) across the edge
                                // opposite vertex k (the reference's adjDT(k), DV:656-669)
   int* loc;                    // per point: slot of a triangle near/containing it, -1 = inserted
+  const int* plist;            // points taking part in this round (the current insertion level), or
+                               // null = all points; thread i of the locate kernels handles plist[i]
+  int n_plist;
+  const int* prev;             // per point: nearest point to the left (internal order) of a coarser level
+  int level_thr;               // coarseness of the current level
+  int level_max;               // coarsest class K
   u64* winner;                 // per triangle: min over its points of (priority << 32 | point)
   int* rank;                   // per triangle: exclusive scan of "splits this round"
   int n_tri;                   // triangles alive at the start of the round
@@ -172,9 +178,43 @@ FM_HD inline void queue_active(const DtCtx& c, int t, int stamp) {
 // DV:303-317: a visibility walk from the remembered slot to the triangle that
 // contains the point (three orient tests per step, the edge just crossed is
 // not re-tested), then a vote for that triangle.
+// ------------------------------------------------------------ insertion levels
+// Points are inserted in O(log N) LEVELS of geometrically growing size (a biased randomised
+// insertion order): class(p) = min(K, clz(hash(id)) / 2), so a quarter of the points of class
+// >= k is of class >= k+1; classes are processed from K down to 0.  Only the points of the
+// current level walk and vote, and they start their walk at a triangle incident to the
+// nearest ALREADY INSERTED point to their left in the space-filling-curve order (prev[]),
+// a few triangles away from the answer.  The reference instead re-locates every uninserted
+// point after every insertion (DV:303-317).
+FM_HD inline int clz32(unsigned v) {
+#if defined(__CUDA_ARCH__)
+  return __clz((int)v);
+#else
+  int n = 0;
+  if (v == 0) return 32;
+  while (!(v & 0x80000000u)) { v <<= 1; n++; }
+  return n;
+#endif
+}
+FM_HD inline int point_class(long long id, int K) {
+  int c = clz32(hash32((unsigned)id ^ 0x9e3779b9u)) >> 1;
+  return c < K ? c : K;
+}
+
+// One thread per point of the level: choose the start slot of its walk.
+struct KLevelInit {
+  FM_HD static void run(const DtCtx& c, int i) {
+    int p = c.plist[i];
+    if (c.loc[p] < 0) return;  // a bootstrap vertex
+    int j = c.prev[p];
+    c.loc[p] = j >= 0 ? c.v2t[j] : 0;
+  }
+};
+
 template <bool EXACT>
 struct KLocateVoteT {
-  FM_HD static void run(const DtCtx& c, int p) {
+  FM_HD static void run(const DtCtx& c, int i) {
+    int p = c.plist ? c.plist[i] : i;
     int t = c.loc[p];
     if (t < 0) return;
     int qi;
@@ -192,7 +232,7 @@ struct KLocateVoteT {
       else if ((a.z >> 2) != from && (s = orient_t<EXACT>(pa, pb, q, ia, ib, qi)) <= 0) next = a.z >> 2;
       if (!EXACT && s == 0) {  // inconclusive: the exact kernel resumes the walk from here
         c.loc[p] = t;
-        defer_item(c, p);
+        defer_item(c, i);
         return;
       }
       if (next < 0) break;
@@ -201,6 +241,11 @@ struct KLocateVoteT {
       if (++steps > (1 << 20)) { *c.err |= FM_E_WALK; return; }
     }
     c.loc[p] = t;
+#ifdef FM_COUNT_STEPS
+    FM_ATOMIC_ADD32(&c.counters[12], steps + 1);
+    FM_ATOMIC_ADD32(&c.counters[13], 1);
+    if (steps > 30) FM_ATOMIC_ADD32(&c.counters[14], 1);
+#endif
     u64 key = ((u64)hash32((unsigned)qi) << 32) | (unsigned)p;
     FM_ATOMIC_MIN64(&c.winner[t], key);
   }

@@ -30,6 +30,7 @@ template <class K> struct KName { static const char* get() { return "kernel"; } 
 FM_KNAME(KLocateVote, "locate_exact")
 FM_KNAME(KLocateVoteT<false>, "locate_vote")
 FM_KNAME(KSplitFlag, "split_flag")
+FM_KNAME(KLevelInit, "level_init")
 FM_KNAME(KSplit, "split13")
 FM_KNAME(KCheck, "check_exact")
 FM_KNAME(KCheckT<false>, "flip_check")
@@ -62,6 +63,10 @@ struct fm_handle {
   // generators (internal order) and the permutation
   P4* pts = nullptr;
   int *orig = nullptr, *inv = nullptr;
+  // insertion levels: points sorted by (level, internal index), level offsets (host), scratch
+  int *lvl_order = nullptr, *prev = nullptr;
+  int lvl_K = 0;
+  std::vector<int> lvl_off;
   // triangulation
   I4 *tri = nullptr, *adj = nullptr;
   int *loc = nullptr, *rankbuf = nullptr, *flip_edge = nullptr, *role = nullptr, *amark = nullptr;
@@ -244,6 +249,16 @@ struct CudaBackend {
   }
   P3 fetch_point(const DtCtx& c, int i) { P4 q = fetch4(c, i); return P3{q.x, q.y, q.z}; }
   int fetch_orig(const DtCtx& c, int i) { return (int)fetch4(c, i).id; }
+  struct MaxOp {
+    __host__ __device__ int operator()(int a, int b) const { return a > b ? a : b; }
+  };
+  void prev_coarser(const DtCtx& c, int thr, int* prev) {
+    h->prof_begin();
+    fm_prev_keys<<<(c.n + 255) / 256, 256, 0, h->stream>>>(c.n, c.pts, c.level_max, thr, prev);
+    size_t bytes = h->cub_bytes;
+    h->note_cuda(cub::DeviceScan::InclusiveScan(h->cub_tmp, bytes, prev, prev, MaxOp(), c.n, h->stream), "prev scan");
+    h->prof_end("prev_coarser", c.n);
+  }
   void write_tris(const DtCtx& c, int t0, int cnt, const I4* tri, const I4* adj) {
     cudaMemcpyAsync(c.tri + t0, tri, sizeof(I4) * cnt, cudaMemcpyHostToDevice, h->stream);
     cudaMemcpyAsync(c.adj + t0, adj, sizeof(I4) * cnt, cudaMemcpyHostToDevice, h->stream);
@@ -333,6 +348,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(cudaMallocHost((void**)&h->pinned, 64 * sizeof(int)));
   A(dalloc(&h->pts, h->n_pad));
   A(dalloc(&h->orig, n)); A(dalloc(&h->inv, n)); A(dalloc(&h->v2t, n));
+  A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n));
   A(dalloc(&h->tri, T)); A(dalloc(&h->adj, T)); A(dalloc(&h->cc, T));
   A(dalloc(&h->loc, n)); A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T));
@@ -362,6 +378,9 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
                                   (int*)nullptr, (int)T, 0, 32, h->stream);
   h->cub_bytes = sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
   if (tsort_bytes > h->cub_bytes) h->cub_bytes = tsort_bytes;
+  size_t pscan_bytes = 0;
+  cub::DeviceScan::InclusiveScan(nullptr, pscan_bytes, h->prev, h->prev, CudaBackend::MaxOp(), n, h->stream);
+  if (pscan_bytes > h->cub_bytes) h->cub_bytes = pscan_bytes;
   A(cudaMalloc(&h->cub_tmp, h->cub_bytes));
   int nb = (n + 255) / 256;
   if (lonlat) {
@@ -385,6 +404,22 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(cudaStreamSynchronize(h->stream));
   A(cudaGetLastError());
   h->n_launch += 4;
+  {  // insertion levels: stable sort of the internal indices by level
+    int K = dt_level_count(n);
+    h->lvl_K = K;
+    h->lvl_off.assign(K + 2, 0);
+    unsigned *lk = (unsigned*)k0, *lk2 = (unsigned*)k1;
+    int* doff = nullptr;
+    A(dalloc(&doff, K + 2));
+    fm_level_keys<<<nb, 256, 0, h->stream>>>(n, h->pts, K, lk, i0);
+    bytes = h->cub_bytes;
+    A(cub::DeviceRadixSort::SortPairs(h->cub_tmp, bytes, lk, lk2, i0, h->lvl_order, n, 0, 4, h->stream));
+    fm_level_offsets<<<1, 32, 0, h->stream>>>(n, lk2, K, doff);
+    A(cudaMemcpyAsync(h->lvl_off.data(), doff, sizeof(int) * (K + 2), cudaMemcpyDeviceToHost, h->stream));
+    A(cudaStreamSynchronize(h->stream));
+    cudaFree(doff);
+    h->n_launch += 3;
+  }
   cudaFree(k0); cudaFree(k1); cudaFree(i0); cudaFree(dup);
   if (hdup != big) {
     cudaMemcpy(&o1, h->orig + hdup, sizeof(int), cudaMemcpyDeviceToHost);
@@ -410,7 +445,7 @@ extern "C" int fm_create_dist(int32_t n, const double* x, const double* y, const
 extern "C" void fm_destroy(fm_handle* h) {
   if (!h) return;
   if (h->stream) cudaStreamSynchronize(h->stream);
-  void* ptrs[] = {h->pts, h->orig, h->inv, h->v2t, h->tri, h->adj, h->loc, h->rankbuf, h->flip_edge,
+  void* ptrs[] = {h->pts, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->tri, h->adj, h->loc, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->counters, h->err, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cc, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
@@ -507,7 +542,8 @@ static int triangulate_cold(fm_handle* h) {
   fm_init_loc<<<(h->n + 255) / 256, 256, 0, h->stream>>>(h->n, h->loc, boot[0], boot[1], boot[2], boot[3]);
   h->n_launch++;
   DtStats st;
-  int rc = dt_run(be, c, h->listA, h->listB, &h->stamp, &st, h->errmsg, sizeof h->errmsg);
+  int rc = dt_run(be, c, h->listA, h->listB, h->lvl_order, h->lvl_off.data(), h->lvl_K, h->prev, boot, &h->stamp, &st,
+                  h->errmsg, sizeof h->errmsg);
   if (h->cuda_failed || rc) return 1;
   h->n_tri = c.n_tri;
   if (h->n_tri != 2 * h->n - 4) { h->fail("triangle count %d != 2N-4", h->n_tri); return 1; }
@@ -820,6 +856,12 @@ extern "C" int fm_profile_get(fm_handle* h, int32_t cap, char (*names)[32], int6
   *rows = k;
   return 0;
 }
+#ifdef FM_COUNT_STEPS
+extern "C" int fm_debug_counters(fm_handle* h, int32_t* out) {
+  cudaMemcpy(out, h->counters, 16 * sizeof(int), cudaMemcpyDeviceToHost);
+  return 0;
+}
+#endif
 extern "C" int fm_device_info(char* name, int32_t cap, int32_t* sms) {
   cudaDeviceProp p;
   int dev = 0;

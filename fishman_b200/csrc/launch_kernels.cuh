@@ -147,6 +147,27 @@ __global__ void fm_remap_v2t(int n, const int* newid, int* v2t) {
   if (i < n) v2t[i] = newid[v2t[i]];
 }
 
+// ---- insertion levels (dt_kernels.cuh, "insertion levels")
+__global__ void fm_level_keys(int n, const P4* pts, int K, unsigned* key, int* idx) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { key[i] = (unsigned)(K - point_class(pts[i].id, K)); idx[i] = i; }
+}
+// off[L] = first position of level L in the sorted keys (L = 0 .. K+1)
+__global__ void fm_level_offsets(int n, const unsigned* sorted_key, int K, int* off) {
+  int L = threadIdx.x;
+  if (L > K + 1) return;
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (sorted_key[mid] < (unsigned)L) lo = mid + 1; else hi = mid;
+  }
+  off[L] = lo;
+}
+__global__ void fm_prev_keys(int n, const P4* pts, int K, int thr, int* prev) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) prev[i] = point_class(pts[i].id, K) > thr ? i : -1;
+}
+
 __global__ void fm_morton_keys(int n, const double* x, const double* y, const double* z, u64* key,
                                int* idx) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -54,6 +54,13 @@ struct HostBackend {
       c.v2t[tri[i].x] = c.v2t[tri[i].y] = c.v2t[tri[i].z] = t0 + i;
     }
   }
+  void prev_coarser(const DtCtx& c, int thr, int* prev) {
+    int last = -1;
+    for (int i = 0; i < c.n; i++) {
+      if (point_class(c.pts[i].id, c.level_max) > thr) last = i;
+      prev[i] = last;
+    }
+  }
   int flip_loop(DtCtx& c, int* list[2], int cur, bool skip_check, int* stamp, DtStats* st, char* msg,
                 size_t msglen, int) {
     return dt_flip_loop_host(*this, c, list, cur, skip_check, stamp, st, msg, msglen);
@@ -97,7 +104,17 @@ extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_
   for (int k = 0; k < 4; k++) loc[boot[k]] = -1;
   DtStats st;
   int stamp = 1;
-  if (dt_run(be, c, listA.data(), listB.data(), &stamp, &st, g_err, sizeof g_err)) return 1;
+  int K = dt_level_count(n);
+  std::vector<int> order(n), off(K + 2, 0), prev(n);
+  std::iota(order.begin(), order.end(), 0);
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+    return point_class(pts[a].id, K) > point_class(pts[b].id, K);  // level = K - class, ascending
+  });
+  for (int i = 0; i < n; i++) off[K - point_class(pts[i].id, K) + 1]++;
+  for (int L = 0; L <= K; L++) off[L + 1] += off[L];
+  if (dt_run(be, c, listA.data(), listB.data(), order.data(), off.data(), K, prev.data(), boot, &stamp, &st,
+             g_err, sizeof g_err))
+    return 1;
   if (c.n_tri != T) { snprintf(g_err, sizeof g_err, "triangle count %d != 2n-4", c.n_tri); return 1; }
   for (int t = 0; t < T; t++)
     for (int k = 0; k < 3; k++) {
