@@ -212,10 +212,9 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
            int* prev, const int boot[4], int* stamp, DtStats* st, char* msg, size_t msglen) {
   c.n_tri = 4;
   memset(st, 0, sizeof *st);
-  int zero[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, host[8];
+  int zero[15] = {0}, host[8];
   int* list[2] = {listA, listB};
-  be.write_ints(c.counters, zero, 7);
-  be.write_ints(c.counters + 8, zero, 1);
+  be.write_ints(c.counters, zero, 15);
   int boot_class[4];
   for (int k = 0; k < 4; k++) boot_class[k] = point_class(be.fetch_orig(c, boot[k]), K);
   c.level_max = K;
@@ -269,11 +268,10 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
 template <class B>
 int dt_repair_async(B& be, DtCtx& c, int* listA, int* listB, int* stamp, DtStats* st, char* msg,
                     size_t msglen) {
-  int zero[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  int zero[15] = {0};
   int* list[2] = {listA, listB};
   memset(st, 0, sizeof *st);
-  be.write_ints(c.counters, zero, 7);
-  be.write_ints(c.counters + 8, zero, 1);
+  be.write_ints(c.counters, zero, 15);
   c.stamp = *stamp;
   c.next_active = list[0];
   c.qcount = c.counters;

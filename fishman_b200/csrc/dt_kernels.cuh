@@ -49,6 +49,16 @@ inline T fm_host_exch(T* p, T v) { T o = *p; *p = v; return o; }
 typedef unsigned long long u64;
 static const u64 kNone64 = ~0ULL;
 
+// slots of DtCtx::counters (16 ints; [0..14] are cleared together at the start of a build or
+// repair, the stamp survives)
+enum {
+  FM_C_SLOW = 8,       // deferred items of a filtered launch
+  FM_C_SLOWDONE = 9,   // blocks of the deferred kernel that have finished (self-reset)
+  FM_C_MAXDISP = 10,   // 64-bit word: bits of the largest chord displacement ([10], [11])
+  FM_C_ERR = 12,       // error bits (DtCtx::err points here in the CUDA library)
+  FM_C_STAMP = 15      // next unused stamp
+};
+
 // error bits reported through DtCtx::err
 enum { FM_E_WALK = 1, FM_E_TOPOLOGY = 2, FM_E_OVERFLOW = 4 };
 
@@ -79,7 +89,7 @@ struct DtCtx {
   int n_tri;                   // triangles alive at the start of the round
   // flip rounds
   int stamp;                   // global sub-round counter (>= 1)
-  const int* stamp_dev;        // when non-null the device-resident stamp (counters[7]) overrides
+  const int* stamp_dev;        // when non-null the device-resident stamp (counters[FM_C_STAMP]) overrides
                                // `stamp` at kernel entry: the flip loop advances it on the device
   u64* vote;                   // per triangle: (~stamp << 32 | voter) claimed by atomicMin
   int* flip_edge;              // per active triangle: edge it wants to flip, -1 none
@@ -92,7 +102,7 @@ struct DtCtx {
   int* qcount;                 // length of next_active (one of counters[0], counters[1])
   int* counters;               // [0],[1] queue lengths (ping-pong), [2] flips, [3] turned-over
                                // triangles, [4] splits, [5] flip sub-rounds, [6] largest queue,
-                               // [7] next unused stamp (device-resident copy)
+                               // then see FM_C_* below
   int* slow;                   // items whose fp64 filter was inconclusive (length in counters[8]);
                                // a second launch runs the exact predicates on them
   int* err;
@@ -162,7 +172,7 @@ FM_HD inline u64 morton_key(double x, double y, double z) {
 }
 
 FM_HD inline void defer_item(const DtCtx& c, int item) {
-  int pos = FM_ATOMIC_ADD32(&c.counters[8], 1);
+  int pos = FM_ATOMIC_ADD32(&c.counters[FM_C_SLOW], 1);
   c.slow[pos] = item;
 }
 

@@ -84,6 +84,11 @@ struct fm_handle {
   int *deg = nullptr, *ring_tri = nullptr, *ring_nbr = nullptr;
   int *ecount = nullptr, *de = nullptr, *ve_vvt = nullptr, *ve_vc = nullptr;
   double* stage = nullptr;  // 3n doubles: input-order staging of fm_get/set_generators
+  // the warm Lloyd iteration as a CUDA graph (reset, sweep, deferred sweep, flip loop, centroid,
+  // readback copy): one launch call per iteration instead of seven
+  cudaGraphExec_t warm_graph = nullptr;
+  fm_density warm_graph_rho = {};
+  bool graph_disabled = false;
   // accounting
   long long n_launch = 0, n_cold = 0, n_warm = 0, tot_rounds = 0, tot_sub = 0, tot_flips = 0;
   int max_active = 0;
@@ -164,7 +169,7 @@ struct fm_handle {
     DtCtx c;
     memset(&c, 0, sizeof c);
     c.n = n; c.pts = pts; c.v2t = v2t; c.tri = tri; c.adj = adj; c.loc = loc;
-    c.winner = winner; c.rank = rankbuf; c.n_tri = n_tri; c.stamp = stamp; c.stamp_dev = counters + 7;
+    c.winner = winner; c.rank = rankbuf; c.n_tri = n_tri; c.stamp = stamp; c.stamp_dev = counters + FM_C_STAMP;
     c.vote = vote; c.flip_edge = flip_edge; c.role = role; c.mailbox = mailbox; c.amark = amark;
     c.counters = counters; c.qcount = counters; c.err = err; c.slow = rankbuf;
     return c;
@@ -177,7 +182,7 @@ struct fm_handle {
     c.deg = deg; c.ring_tri = ring_tri; c.ring_nbr = ring_nbr;
     if (rho) c.rho = *rho;
     c.cell_begin = blk_begin; c.cell_end = blk_begin + blk_count;
-    c.maxdisp = scratch64; c.err = err;
+    c.maxdisp = (u64*)(counters + FM_C_MAXDISP); c.err = err;
     return c;
   }
 };
@@ -195,7 +200,6 @@ struct CudaBackend {
     fm_kernel_deferred<K<true>><<<h->sms * 4, 128, 0, h->stream>>>(c);
     h->note_cuda(cudaGetLastError(), KName<K<true>>::get());
     h->prof_end(KName<K<true>>::get(), 0);
-    h->note_cuda(cudaMemsetAsync(c.counters + 8, 0, sizeof(int), h->stream), "deferred reset");
   }
   void fill64(u64* p, u64 v, size_t n) {
     // only all-ones is ever requested: a byte memset does it
@@ -352,15 +356,16 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(dalloc(&h->tri, T)); A(dalloc(&h->adj, T)); A(dalloc(&h->cc, T));
   A(dalloc(&h->loc, n)); A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T));
-  A(dalloc(&h->counters, 16)); A(dalloc(&h->err, 1));
+  A(dalloc(&h->counters, 16));
+  h->err = h->counters + FM_C_ERR;
   A(dalloc(&h->winner, T)); A(dalloc(&h->vote, T)); A(dalloc(&h->mailbox, 3 * T)); A(dalloc(&h->scratch64, 4));
   A(cudaMemsetAsync(h->vote, 0xff, sizeof(u64) * T, h->stream));
   A(cudaMemsetAsync(h->role, 0, sizeof(int) * T, h->stream));
   A(cudaMemsetAsync(h->amark, 0, sizeof(int) * T, h->stream));
   A(cudaMemsetAsync(h->mailbox, 0, sizeof(u64) * 3 * T, h->stream));
-  A(cudaMemsetAsync(h->err, 0, sizeof(int), h->stream));
   A(cudaMemsetAsync(h->pts, 0, sizeof(P4) * h->n_pad, h->stream));
-  int init_counters[16] = {0, 0, 0, 0, 0, 0, 0, 1};  // [7]: first stamp
+  int init_counters[16] = {0};
+  init_counters[FM_C_STAMP] = 1;  // first stamp
   A(cudaMemcpyAsync(h->counters, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, h->stream));
   A(cudaStreamSynchronize(h->stream));
   // staging: input order coordinates, keys, sort buffers
@@ -446,7 +451,7 @@ extern "C" void fm_destroy(fm_handle* h) {
   if (!h) return;
   if (h->stream) cudaStreamSynchronize(h->stream);
   void* ptrs[] = {h->pts, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->tri, h->adj, h->loc, h->rankbuf, h->flip_edge,
-                  h->role, h->amark, h->listA, h->listB, h->counters, h->err, h->winner, h->vote,
+                  h->role, h->amark, h->listA, h->listB, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cc, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
   for (void* p : ptrs)
@@ -456,6 +461,7 @@ extern "C" void fm_destroy(fm_handle* h) {
   if (h->ev1) cudaEventDestroy(h->ev1);
   for (auto& p : h->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
   for (auto e : h->ev_pool) cudaEventDestroy(e);
+  if (h->warm_graph) cudaGraphExecDestroy(h->warm_graph);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -465,20 +471,23 @@ extern "C" const char* fm_last_error(const fm_handle* h) { return h ? h->errmsg 
 // One readback for everything the host needs after a batch of launches: the eight counters,
 // the error bits and the displacement word.  Synchronises the stream.
 struct Readback {
-  int counters[8];
+  int counters[16];
   int err;
+  int stamp;
   double maxdisp;
 };
-static int readback(fm_handle* h, Readback* r, const char* where) {
+static cudaError_t readback_enqueue(fm_handle* h) {
+  return cudaMemcpyAsync(h->pinned + 16, h->counters, 16 * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
+}
+static int readback(fm_handle* h, Readback* r, const char* where, bool enqueued = false) {
   if (h->cuda_failed) return 1;
-  cudaError_t e = cudaMemcpyAsync(h->pinned, h->counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(h->pinned + 8, h->err, sizeof(int), cudaMemcpyDeviceToHost, h->stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(h->pinned + 10, h->scratch64, sizeof(u64), cudaMemcpyDeviceToHost, h->stream);
+  cudaError_t e = enqueued ? cudaSuccess : readback_enqueue(h);
   if (e == cudaSuccess) e = h->sync();
   if (e != cudaSuccess) { h->cuda_failed = true; h->fail("CUDA error in %s: %s", where, cudaGetErrorString(e)); return 1; }
-  memcpy(r->counters, h->pinned, sizeof r->counters);
-  r->err = h->pinned[8];
-  memcpy(&r->maxdisp, h->pinned + 10, sizeof(double));
+  memcpy(r->counters, h->pinned + 16, sizeof r->counters);
+  r->err = r->counters[FM_C_ERR];
+  r->stamp = r->counters[FM_C_STAMP];
+  memcpy(&r->maxdisp, r->counters + FM_C_MAXDISP, sizeof(double));
   if (r->err) {
     cudaMemsetAsync(h->err, 0, sizeof(int), h->stream);
     h->fail("%s: device reported error bits %d (%s%s%s)", where, r->err,
@@ -487,14 +496,14 @@ static int readback(fm_handle* h, Readback* r, const char* where) {
             (r->err & FM_E_OVERFLOW) ? "flip rounds did not terminate" : "");
     return 1;
   }
-  if (r->counters[7] > (1 << 27)) {  // stamps are about to run out: start over with clean words
+  if (r->stamp > (1 << 27)) {  // stamps are about to run out: start over with clean words
     size_t T = 2 * (size_t)h->n - 4;
     int one = 1;
     cudaMemsetAsync(h->vote, 0xff, sizeof(u64) * T, h->stream);
     cudaMemsetAsync(h->role, 0, sizeof(int) * T, h->stream);
     cudaMemsetAsync(h->amark, 0, sizeof(int) * T, h->stream);
     cudaMemsetAsync(h->mailbox, 0, sizeof(u64) * 3 * T, h->stream);
-    cudaMemcpyAsync(h->counters + 7, &one, sizeof(int), cudaMemcpyHostToDevice, h->stream);
+    cudaMemcpyAsync(h->counters + FM_C_STAMP, &one, sizeof(int), cudaMemcpyHostToDevice, h->stream);
     cudaStreamSynchronize(h->stream);
   }
   return 0;
@@ -618,7 +627,7 @@ extern "C" int fm_get_triangles(fm_handle* h, int32_t* tri, int32_t* adj) {
 
 static int bump_stamp(fm_handle* h, int current) {
   int next = current + 1;
-  FM_CUDA(cudaMemcpyAsync(h->counters + 7, &next, sizeof(int), cudaMemcpyHostToDevice, h->stream));
+  FM_CUDA(cudaMemcpyAsync(h->counters + FM_C_STAMP, &next, sizeof(int), cudaMemcpyHostToDevice, h->stream));
   FM_CUDA(cudaStreamSynchronize(h->stream));
   return 0;
 }
@@ -709,7 +718,6 @@ static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded) {
   else { d.cx = d.cy = 0; d.cz = 1; d.beta = 0; d.alpha = 1; d.gamma = 1; }
   VdCtx c = h->vd_ctx(&d);
   c.abort_flag = guarded ? h->counters + 3 : nullptr;
-  cudaMemsetAsync(h->scratch64, 0, sizeof(u64), h->stream);
   int cnt = h->blk_count;
   if (cnt <= 0) return;
   const int B = 128;
@@ -721,15 +729,74 @@ static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded) {
   h->prof_end("centroid_update", cnt);
 }
 
+static bool same_density(const fm_density* a, const fm_density& b) {
+  fm_density d = {};
+  if (a) d = *a;
+  else { d.cz = 1; d.alpha = 1; d.gamma = 1; }
+  return d.kind == b.kind && d.cx == b.cx && d.cy == b.cy && d.cz == b.cz && d.beta == b.beta &&
+         d.alpha == b.alpha && d.gamma == b.gamma;
+}
+
+// Queues one warm iteration (repair + centroid + readback copy) on the stream.  Outside
+// profiling the sequence is captured once into a CUDA graph and replayed; every pointer and
+// size in it is fixed for the life of the handle, the stamp and the queue lengths live on the
+// device.  If capture is not possible the launches are issued directly.
+static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
+  if (!h->profile && !h->graph_disabled) {
+    if (h->warm_graph && !same_density(rho, h->warm_graph_rho)) {
+      cudaGraphExecDestroy(h->warm_graph);
+      h->warm_graph = nullptr;
+    }
+    if (!h->warm_graph) {
+      cudaGraph_t g = nullptr;
+      long long launches_before = h->n_launch;
+      cudaError_t e = cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal);
+      bool ok = (e == cudaSuccess);
+      if (ok) {
+        int rc = repair_async(h);
+        launch_centroid(h, rho, true);
+        cudaError_t e2 = readback_enqueue(h);
+        e = cudaStreamEndCapture(h->stream, &g);
+        ok = (rc == 0 && e2 == cudaSuccess && e == cudaSuccess && g != nullptr && !h->cuda_failed);
+      }
+      if (ok) ok = cudaGraphInstantiate(&h->warm_graph, g, 0) == cudaSuccess;
+      if (g) cudaGraphDestroy(g);
+      h->n_launch = launches_before;
+      if (!ok) {
+        cudaGetLastError();  // clear the capture error; fall back to direct launches for good
+        h->cuda_failed = false;
+        h->errmsg[0] = 0;
+        h->warm_graph = nullptr;
+        h->graph_disabled = true;
+      } else {
+        fm_density d = {};
+        if (rho) d = *rho;
+        else { d.cz = 1; d.alpha = 1; d.gamma = 1; }
+        h->warm_graph_rho = d;
+      }
+    }
+    if (h->warm_graph) {
+      h->n_launch += 4;  // sweep, deferred sweep, flip loop, centroid
+      cudaError_t e = cudaGraphLaunch(h->warm_graph, h->stream);
+      if (e != cudaSuccess) { h->fail("cudaGraphLaunch: %s", cudaGetErrorString(e)); return 1; }
+      return 0;
+    }
+  }
+  if (repair_async(h)) return 1;
+  launch_centroid(h, rho, true);
+  cudaError_t e = readback_enqueue(h);
+  if (e != cudaSuccess) { h->fail("readback: %s", cudaGetErrorString(e)); return 1; }
+  return 0;
+}
+
 // One Lloyd iteration on this rank's block.  Warm: sweep + cooperative flip loop + centroid
 // are queued back to back and the host waits once, for the displacement; if the sweep found
 // a turned-over triangle the device work was skipped and the iteration is redone cold.
 static int lloyd_iteration(fm_handle* h, const fm_density* rho, int warm, double* maxdisp) {
   Readback r;
   if (warm && h->have_dt) {
-    if (repair_async(h)) return 1;
-    launch_centroid(h, rho, true);
-    if (readback(h, &r, "fm_lloyd")) return 1;
+    if (warm_iteration_enqueue(h, rho)) return 1;
+    if (readback(h, &r, "fm_lloyd", true)) return 1;
     if (r.counters[3] == 0) {
       account(h, r, 0);
       h->n_warm++;
@@ -737,7 +804,7 @@ static int lloyd_iteration(fm_handle* h, const fm_density* rho, int warm, double
       *maxdisp = r.maxdisp;
       return 0;
     }
-    if (bump_stamp(h, r.counters[7])) return 1;
+    if (bump_stamp(h, r.stamp)) return 1;
   }
   if (triangulate_cold(h)) return 1;
   if (circumcentres(h, false)) return 1;

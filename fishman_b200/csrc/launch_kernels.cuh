@@ -37,20 +37,26 @@ __global__ void __launch_bounds__(256, KOcc<K>::value) fm_kernel(Ctx c, int n) {
 template <class K>
 __global__ void __launch_bounds__(128) fm_kernel_deferred(DtCtx c) {
   use_device_stamp(c);
-  int m = c.counters[8];
+  int m = c.counters[FM_C_SLOW];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) K::run(c, c.slow[i]);
+  // the last block to finish empties the list for the next filtered launch
+  __syncthreads();
+  if (threadIdx.x == 0 && atomicAdd(&c.counters[FM_C_SLOWDONE], 1) == (int)gridDim.x - 1) {
+    c.counters[FM_C_SLOW] = 0;
+    c.counters[FM_C_SLOWDONE] = 0;
+  }
 }
 
 // All flip sub-rounds of one insertion round (or of one warm repair) in ONE cooperative
 // launch: check -> mark -> flip -> patch over the current queue, grid-wide barrier between
 // phases, until the queue is empty.  No host round trip per sub-round; the stamp lives in
-// counters[7].  The bodies are the same KCheck/KMark/KFlip/KPatch the host-driven loop runs.
+// counters[FM_C_STAMP].  The bodies are the same KCheck/KMark/KFlip/KPatch the host-driven loop runs.
 __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* listB, int cur, int skip_check) {
   cg::grid_group grid = cg::this_grid();
   const int gsz = gridDim.x * blockDim.x, gid = blockIdx.x * blockDim.x + threadIdx.x;
   int* list[2] = {listA, listB};
   volatile int* vc = c.counters;
-  int stamp = vc[7];
+  int stamp = vc[FM_C_STAMP];
   if (vc[3] > 0) return;  // a triangle turned over: leave everything to the rebuild
   int sub = 0, maxq = 0;
   for (;; sub++) {
@@ -79,7 +85,7 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
     stamp++;
   }
   if (gid == 0) {
-    c.counters[7] = stamp;
+    c.counters[FM_C_STAMP] = stamp;
     c.counters[5] += sub;
     if (maxq > c.counters[6]) c.counters[6] = maxq;
   }
@@ -88,7 +94,7 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
 // bookkeeping at the end of a host-driven flip sub-round (what thread 0 of fm_flip_coop does)
 __global__ void fm_subround_end(int* counters, int cur, int nact) {
   counters[cur] = 0;
-  counters[7] += 1;
+  counters[FM_C_STAMP] += 1;
   counters[5] += 1;
   if (nact > counters[6]) counters[6] = nact;
 }

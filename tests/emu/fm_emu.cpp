@@ -22,10 +22,10 @@ struct HostBackend {
   template <template <bool> class K>
   void launch_filtered(const DtCtx& c, int n) {
     for (int i = 0; i < n; i++) K<false>::run(c, i);
-    int m = c.counters[8];
+    int m = c.counters[FM_C_SLOW];
     n_deferred += m;
     for (int i = 0; i < m; i++) K<true>::run(c, c.slow[i]);
-    c.counters[8] = 0;
+    c.counters[FM_C_SLOW] = 0;
   }
   long long n_deferred = 0;
   void fill64(u64* p, u64 v, size_t n) { std::fill(p, p + n, v); }
