@@ -63,8 +63,9 @@ enum {
 enum { FM_E_WALK = 1, FM_E_TOPOLOGY = 2, FM_E_OVERFLOW = 4 };
 
 // Generator record: 32 bytes = one DRAM sector, so that a vertex gather costs one sector
-// instead of four (x, y, z, id in separate arrays).  id = original 0-based id (SoS key).
-struct alignas(16) P4 {
+// instead of four (x, y, z, id in separate arrays) and ONE 256-bit load (LDG.E.ENL2.256 on
+// sm_100a).  id = original 0-based id (SoS key).
+struct alignas(32) P4 {
   double x, y, z;
   long long id;
 };

@@ -346,6 +346,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   A(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fm_flip_coop, 256, 0));
   h->coop_blocks = sms * (per_sm > 0 ? per_sm : 1);
+  if (const char* e = getenv("FM_COOP_BLOCKS")) { int v = atoi(e); if (v > 0 && v <= h->coop_blocks) h->coop_blocks = v; }
   h->sms = sms;
   A(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   A(cudaEventCreate(&h->ev0)); A(cudaEventCreate(&h->ev1));

@@ -103,8 +103,11 @@ __global__ void fm_subround_end(int* counters, int cur, int nact) {
 // ring triangle ids are staged in shared memory, the per-cell chord displacement is reduced
 // with warp shuffles, then once per block through shared memory, and one atomicMax per block
 // reaches HBM.
+#ifndef FM_OCC_CENTROID
+#define FM_OCC_CENTROID 8
+#endif
 template <bool UNIFORM>
-__global__ void __launch_bounds__(128) fm_centroid_update(const VdCtx c, int n) {
+__global__ void __launch_bounds__(128, FM_OCC_CENTROID) fm_centroid_update(const VdCtx c, int n) {
   extern __shared__ int ring_smem[];
   if (c.abort_flag && *c.abort_flag) return;
   int j = blockIdx.x * blockDim.x + threadIdx.x;
