@@ -46,6 +46,12 @@ inline T fm_host_exch(T* p, T v) { T o = *p; *p = v; return o; }
 #define FM_ATOMIC_EXCH32(p, v) fm_host_exch<int>((int*)(p), (int)(v))
 #endif
 
+// One triangle slot: vertex ids and adjacency side by side, 32 bytes = one sector and one
+// 256-bit load for the passes that need both (all of them but the ring walk).
+struct alignas(32) Row {
+  I4 v, a;
+};
+
 typedef unsigned long long u64;
 static const u64 kNone64 = ~0ULL;
 
@@ -75,8 +81,8 @@ struct DtCtx {
   P4* pts;                     // internal (space-filling-curve) order
   int* v2t;                    // per vertex: SOME incident triangle (ring start), kept by split/flip
   P4* cc;                      // circumcentres per triangle, maintained by sweep/flip when non-null
-  I4* tri;                     // vertices (x,y,z), CCW seen from outside; w unused
-  I4* adj;                     // adj[k] = (neighbour << 2 | its edge index) across the edge
+  Row* row;                    // per triangle slot: v = vertices (x,y,z), CCW seen from outside;
+                               // a[k] = (neighbour << 2 | its edge index) across the edge
                                // opposite vertex k (the reference's adjDT(k), DV:656-669)
   int* loc;                    // per point: slot of a triangle near/containing it, -1 = inserted
   const int* plist;            // points taking part in this round (the current insertion level), or
@@ -232,8 +238,8 @@ struct KLocateVoteT {
     P3 q = ldv(c, p, qi);
     int from = -1, steps = 0;
     for (;;) {
-      I4 v = c.tri[t];
-      I4 a = c.adj[t];
+      Row r = c.row[t];
+      I4 v = r.v, a = r.a;
       int ia, ib, ic;
       P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
       int next = -1, s = 1;
@@ -284,8 +290,8 @@ struct KSplit {
     u64 w = c.winner[t];
     if (w == kNone64) return;
     int p = (int)(w & 0xffffffffULL);
-    I4 v = c.tri[t];
-    I4 a = c.adj[t];
+    Row r = c.row[t];
+    I4 v = r.v, a = r.a;
     int s1 = c.n_tri + 2 * c.rank[t], s2 = s1 + 1;
     int childOf[3] = {s1, s2, t};  // parent edge k -> child slot
     int outer[3];
@@ -295,15 +301,12 @@ struct KSplit {
         outer[k] = enc(child_slot(c, n, e), 2);
       } else {
         outer[k] = ne;
-        ((int*)&c.adj[n])[e] = enc(childOf[k], 2);
+        ((int*)&c.row[n].a)[e] = enc(childOf[k], 2);
       }
     }
-    c.tri[t] = I4{v.x, v.y, p, 0};
-    c.adj[t] = I4{enc(s1, 1), enc(s2, 0), outer[2], 0};
-    c.tri[s1] = I4{v.y, v.z, p, 0};
-    c.adj[s1] = I4{enc(s2, 1), enc(t, 0), outer[0], 0};
-    c.tri[s2] = I4{v.z, v.x, p, 0};
-    c.adj[s2] = I4{enc(t, 1), enc(s1, 0), outer[1], 0};
+    c.row[t] = Row{I4{v.x, v.y, p, 0}, I4{enc(s1, 1), enc(s2, 0), outer[2], 0}};
+    c.row[s1] = Row{I4{v.y, v.z, p, 0}, I4{enc(s2, 1), enc(t, 0), outer[0], 0}};
+    c.row[s2] = Row{I4{v.z, v.x, p, 0}, I4{enc(t, 1), enc(s1, 0), outer[1], 0}};
     c.loc[p] = -1;
     c.v2t[p] = t;
     c.v2t[v.z] = s1;  // the only vertex that left slot t
@@ -328,14 +331,14 @@ template <bool EXACT>
 struct KCheckT {
   FM_HD static void run(const DtCtx& c, int i) {
     int t = c.active[i];
-    I4 v = c.tri[t];
-    I4 a = c.adj[t];
+    Row r = c.row[t];
+    I4 v = r.v, a = r.a;
     int ia, ib, ic, idd;
     P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
     int fe = -1;
     for (int k = 0; k < 3; k++) {
       int ne = geti(a, k), n = ne >> 2, e = ne & 3;
-      int d = ((const int*)c.tri)[4 * (size_t)n + e];
+      int d = ((const int*)c.row)[8 * (size_t)n + e];
       P3 pd = ldv(c, d, idd);
       int s = incircle_t<EXACT>(pa, pb, pc, pd, ia, ib, ic, idd);
       if (!EXACT && s == 0) { defer_item(c, i); return; }
@@ -360,16 +363,16 @@ typedef KCheckT<true> KCheck;
 template <bool EXACT>
 struct KSweepT {
   FM_HD static void run(const DtCtx& c, int t) {
-    I4 v = c.tri[t];
-    I4 a = c.adj[t];
+    Row r = c.row[t];
+    I4 v = r.v, a = r.a;
     // stage 1: everything that depends only on the two rows -- three vertex records and the
     // three opposite-vertex ids -- is requested before anything is consumed
     P4 qa = c.pts[v.x], qb = c.pts[v.y], qc = c.pts[v.z];
-    const int* trow = (const int*)c.tri;
+    const int* trow = (const int*)c.row;
     int n0 = a.x >> 2, n1 = a.y >> 2, n2 = a.z >> 2;
-    int d0 = n0 > t ? trow[4 * (size_t)n0 + (a.x & 3)] : -1;
-    int d1 = n1 > t ? trow[4 * (size_t)n1 + (a.y & 3)] : -1;
-    int d2 = n2 > t ? trow[4 * (size_t)n2 + (a.z & 3)] : -1;
+    int d0 = n0 > t ? trow[8 * (size_t)n0 + (a.x & 3)] : -1;
+    int d1 = n1 > t ? trow[8 * (size_t)n1 + (a.y & 3)] : -1;
+    int d2 = n2 > t ? trow[8 * (size_t)n2 + (a.z & 3)] : -1;
     // stage 2: the opposite vertices
     P4 z = {0, 0, 0, 0};
     P4 q0 = d0 >= 0 ? c.pts[d0] : z;
@@ -419,7 +422,7 @@ struct KMark {
     int t = c.active[i];
     int fe = c.flip_edge[t];
     if (fe < 0) return;
-    int n = geti(c.adj[t], fe) >> 2;
+    int n = geti(c.row[t].a, fe) >> 2;
     u64 key = vote_key(c.stamp, t);
     if (c.vote[t] == key && c.vote[n] == key) {
       c.role[t] = (c.stamp << 2) | 1;
@@ -457,9 +460,11 @@ struct KFlip {
     int t = c.active[i];
     if (c.role[t] != ((c.stamp << 2) | 1)) return;
     int k = c.flip_edge[t];
-    I4 vt = c.tri[t], at = c.adj[t];
+    Row rt = c.row[t];
+    I4 vt = rt.v, at = rt.a;
     int ne = geti(at, k), n = ne >> 2, e = ne & 3;
-    I4 vn = c.tri[n], an = c.adj[n];
+    Row rn = c.row[n];
+    I4 vn = rn.v, an = rn.a;
     FlipGeom g = flip_geom(t, k, n, e);
     int va = geti(vt, k), vb = geti(vt, (k + 1) % 3), vc = geti(vt, (k + 2) % 3), vd = geti(vn, e);
     int outer[4];
@@ -471,13 +476,11 @@ struct KFlip {
       if ((c.role[m] >> 2) == c.stamp) {
         c.mailbox[3 * (size_t)m + em] = ((u64)(unsigned)c.stamp << 32) | (unsigned)nw;
       } else {
-        ((int*)&c.adj[m])[em] = nw;
+        ((int*)&c.row[m].a)[em] = nw;
       }
     }
-    c.tri[t] = I4{va, vb, vd, e};  // w keeps e for KPatch
-    c.adj[t] = I4{outer[2], enc(n, 2), outer[0], 0};
-    c.tri[n] = I4{va, vd, vc, 0};
-    c.adj[n] = I4{outer[3], outer[1], enc(t, 1), 0};
+    c.row[t] = Row{I4{va, vb, vd, e}, I4{outer[2], enc(n, 2), outer[0], 0}};  // v.w keeps e for KPatch
+    c.row[n] = Row{I4{va, vd, vc, 0}, I4{outer[3], outer[1], enc(t, 1), 0}};
     c.v2t[vb] = t;  // b left slot n, c left slot t (a and d only gained a triangle)
     c.v2t[vc] = n;
     if (c.cc) {
@@ -496,18 +499,18 @@ struct KFlip {
 
 // After all flips of the sub-round: a pair whose outer neighbour flipped too
 // finds that neighbour's new (slot, edge) in the mailbox of its OLD (slot, edge).
-// The pre-flip indices come back from flip_edge[t] (k) and tri[t].w (e).
+// The pre-flip indices come back from flip_edge[t] (k) and row[t].v.w (e).
 struct KPatch {
   FM_HD static void run(const DtCtx& c, int i) {
     int t = c.active[i];
     if (c.role[t] != ((c.stamp << 2) | 1)) return;
     int k = c.flip_edge[t];
-    int n = c.adj[t].y >> 2;
-    int e = c.tri[t].w;
+    int n = c.row[t].a.y >> 2;
+    int e = c.row[t].v.w;
     FlipGeom g = flip_geom(t, k, n, e);
     for (int j = 0; j < 4; j++) {
       u64 msg = c.mailbox[3 * (size_t)g.so[j] + g.io[j]];
-      if ((int)(msg >> 32) == c.stamp) ((int*)&c.adj[g.sn[j]])[g.in[j]] = (int)(msg & 0xffffffffULL);
+      if ((int)(msg >> 32) == c.stamp) ((int*)&c.row[g.sn[j]].a)[g.in[j]] = (int)(msg & 0xffffffffULL);
     }
   }
 };
@@ -519,7 +522,7 @@ struct KPatch {
 // not strictly CCW any more (counters[3]).
 struct KValidate {
   FM_HD static void run(const DtCtx& c, int t) {
-    I4 v = c.tri[t];
+    I4 v = c.row[t].v;
     int ia, ib, ic;
     P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
     if (orient(pa, pb, pc, ia, ib, ic) <= 0)

@@ -68,7 +68,7 @@ struct fm_handle {
   int lvl_K = 0;
   std::vector<int> lvl_off;
   // triangulation
-  I4 *tri = nullptr, *adj = nullptr;
+  Row* rows = nullptr;
   int *loc = nullptr, *rankbuf = nullptr, *flip_edge = nullptr, *role = nullptr, *amark = nullptr;
   int *listA = nullptr, *listB = nullptr, *counters = nullptr, *err = nullptr, *v2t = nullptr;
   u64 *winner = nullptr, *vote = nullptr, *mailbox = nullptr, *scratch64 = nullptr;
@@ -168,7 +168,7 @@ struct fm_handle {
   DtCtx dt_ctx() {
     DtCtx c;
     memset(&c, 0, sizeof c);
-    c.n = n; c.pts = pts; c.v2t = v2t; c.tri = tri; c.adj = adj; c.loc = loc;
+    c.n = n; c.pts = pts; c.v2t = v2t; c.row = rows; c.loc = loc;
     c.winner = winner; c.rank = rankbuf; c.n_tri = n_tri; c.stamp = stamp; c.stamp_dev = counters + FM_C_STAMP;
     c.vote = vote; c.flip_edge = flip_edge; c.role = role; c.mailbox = mailbox; c.amark = amark;
     c.counters = counters; c.qcount = counters; c.err = err; c.slow = rankbuf;
@@ -177,7 +177,7 @@ struct fm_handle {
   VdCtx vd_ctx(const Density* rho) {
     VdCtx c;
     memset(&c, 0, sizeof c);
-    c.n = n; c.n_tri = n_tri; c.pts = pts; c.tri = tri; c.adj = adj;
+    c.n = n; c.n_tri = n_tri; c.pts = pts; c.row = rows;
     c.cc = cc; c.cclon = cclon; c.cclat = cclat; c.v2t = v2t;
     c.deg = deg; c.ring_tri = ring_tri; c.ring_nbr = ring_nbr;
     if (rho) c.rho = *rho;
@@ -264,8 +264,10 @@ struct CudaBackend {
     h->prof_end("prev_coarser", c.n);
   }
   void write_tris(const DtCtx& c, int t0, int cnt, const I4* tri, const I4* adj) {
-    cudaMemcpyAsync(c.tri + t0, tri, sizeof(I4) * cnt, cudaMemcpyHostToDevice, h->stream);
-    cudaMemcpyAsync(c.adj + t0, adj, sizeof(I4) * cnt, cudaMemcpyHostToDevice, h->stream);
+    std::vector<Row> rows(cnt);
+    for (int i = 0; i < cnt; i++) rows[i] = Row{tri[i], adj[i]};
+    cudaMemcpyAsync(c.row + t0, rows.data(), sizeof(Row) * cnt, cudaMemcpyHostToDevice, h->stream);
+    h->note_cuda(h->sync(), "write_tris");
     for (int i = 0; i < cnt; i++) {
       int t = t0 + i;
       const int v[3] = {tri[i].x, tri[i].y, tri[i].z};
@@ -354,7 +356,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(dalloc(&h->pts, h->n_pad));
   A(dalloc(&h->orig, n)); A(dalloc(&h->inv, n)); A(dalloc(&h->v2t, n));
   A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n));
-  A(dalloc(&h->tri, T)); A(dalloc(&h->adj, T)); A(dalloc(&h->cc, T));
+  A(dalloc(&h->rows, T)); A(dalloc(&h->cc, T));
   A(dalloc(&h->loc, n)); A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T));
   A(dalloc(&h->counters, 16));
@@ -451,7 +453,7 @@ extern "C" int fm_create_dist(int32_t n, const double* x, const double* y, const
 extern "C" void fm_destroy(fm_handle* h) {
   if (!h) return;
   if (h->stream) cudaStreamSynchronize(h->stream);
-  void* ptrs[] = {h->pts, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->tri, h->adj, h->loc, h->rankbuf, h->flip_edge,
+  void* ptrs[] = {h->pts, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cc, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
@@ -521,20 +523,17 @@ static int sort_triangles(fm_handle* h) {
   int T = h->n_tri, nb = (T + 255) / 256;
   unsigned *key = (unsigned*)h->flip_edge, *key2 = (unsigned*)h->role;
   int *idx = h->listA, *order = h->listB, *newid = h->amark;
-  I4* tri2 = (I4*)h->mailbox;  // 3T u64 = 24T bytes >= 16T
-  I4* adj2 = (I4*)h->cc;       // 32T bytes; circumcentres are recomputed after every build
+  Row* row2 = (Row*)h->cc;  // 32T bytes; circumcentres are recomputed after every build
   h->prof_begin();
-  fm_tri_keys<<<nb, 256, 0, h->stream>>>(T, h->tri, key, idx);
+  fm_tri_keys<<<nb, 256, 0, h->stream>>>(T, h->rows, key, idx);
   size_t bytes = h->cub_bytes;
   int bits = 1;
   while ((1LL << bits) < h->n) bits++;
   FM_CUDA(cub::DeviceRadixSort::SortPairs(h->cub_tmp, bytes, key, key2, idx, order, T, 0, bits, h->stream));
   fm_tri_newid<<<nb, 256, 0, h->stream>>>(T, order, newid);
-  fm_tri_permute<<<nb, 256, 0, h->stream>>>(T, order, newid, h->tri, h->adj, tri2, adj2);
+  fm_tri_permute<<<nb, 256, 0, h->stream>>>(T, order, newid, h->rows, row2);
   fm_remap_v2t<<<(h->n + 255) / 256, 256, 0, h->stream>>>(h->n, newid, h->v2t);
-  FM_CUDA(cudaMemcpyAsync(h->tri, tri2, sizeof(I4) * T, cudaMemcpyDeviceToDevice, h->stream));
-  FM_CUDA(cudaMemcpyAsync(h->adj, adj2, sizeof(I4) * T, cudaMemcpyDeviceToDevice, h->stream));
-  FM_CUDA(cudaMemsetAsync(h->mailbox, 0, sizeof(u64) * 3 * (size_t)T, h->stream));
+  FM_CUDA(cudaMemcpyAsync(h->rows, row2, sizeof(Row) * T, cudaMemcpyDeviceToDevice, h->stream));
   FM_CUDA(cudaMemsetAsync(h->role, 0, sizeof(int) * T, h->stream));
   FM_CUDA(cudaMemsetAsync(h->amark, 0, sizeof(int) * T, h->stream));
   h->prof_end("sort_triangles", T);
@@ -617,7 +616,7 @@ extern "C" int fm_get_triangles(fm_handle* h, int32_t* tri, int32_t* adj) {
   int *dt = nullptr, *da = nullptr;
   FM_CUDA(dalloc(&dt, 3 * (size_t)T));
   FM_CUDA(dalloc(&da, 3 * (size_t)T));
-  fm_export_tris<<<(T + 255) / 256, 256, 0, h->stream>>>(T, h->tri, h->adj, h->pts, dt, da);
+  fm_export_tris<<<(T + 255) / 256, 256, 0, h->stream>>>(T, h->rows, h->pts, dt, da);
   h->n_launch++;
   if (tri) FM_CUDA(cudaMemcpyAsync(tri, dt, sizeof(int) * 3 * T, cudaMemcpyDeviceToHost, h->stream));
   if (adj) FM_CUDA(cudaMemcpyAsync(adj, da, sizeof(int) * 3 * T, cudaMemcpyDeviceToHost, h->stream));

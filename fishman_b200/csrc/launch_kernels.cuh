@@ -128,10 +128,10 @@ __global__ void __launch_bounds__(128, FM_OCC_CENTROID) fm_centroid_update(const
 // Slots are handed out in creation order, so neighbours on the sphere end up far apart in
 // memory.  Sorting the slots by their smallest vertex index (vertices are in Morton order)
 // makes the per-triangle and per-cell passes of the Lloyd loop gather from nearby rows.
-__global__ void fm_tri_keys(int nt, const I4* tri, unsigned* key, int* idx) {
+__global__ void fm_tri_keys(int nt, const Row* row, unsigned* key, int* idx) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < nt) {
-    I4 v = tri[t];
+    I4 v = row[t].v;
     key[t] = (unsigned)min(v.x, min(v.y, v.z));
     idx[t] = t;
   }
@@ -140,15 +140,13 @@ __global__ void fm_tri_newid(int nt, const int* order, int* newid) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < nt) newid[order[t]] = t;
 }
-__global__ void fm_tri_permute(int nt, const int* order, const int* newid, const I4* tri, const I4* adj,
-                               I4* tri_out, I4* adj_out) {
+__global__ void fm_tri_permute(int nt, const int* order, const int* newid, const Row* row, Row* row_out) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < nt) {
-    int o = order[t];
-    I4 a = adj[o];
-    tri_out[t] = tri[o];
-    adj_out[t] = I4{(newid[a.x >> 2] << 2) | (a.x & 3), (newid[a.y >> 2] << 2) | (a.y & 3),
-                    (newid[a.z >> 2] << 2) | (a.z & 3), 0};
+    Row r = row[order[t]];
+    I4 a = r.a;
+    row_out[t] = Row{r.v, I4{(newid[a.x >> 2] << 2) | (a.x & 3), (newid[a.y >> 2] << 2) | (a.y & 3),
+                             (newid[a.z >> 2] << 2) | (a.z & 3), 0}};
   }
 }
 __global__ void fm_remap_v2t(int n, const int* newid, int* v2t) {
@@ -243,11 +241,10 @@ __global__ void fm_init_loc(int n, int* loc, int b0, int b1, int b2, int b3) {
   if (i < n) loc[i] = (i == b0 || i == b1 || i == b2 || i == b3) ? -1 : 0;
 }
 
-__global__ void fm_export_tris(int nt, const I4* tri, const I4* adj, const P4* pts, int* otri,
-                               int* oadj) {
+__global__ void fm_export_tris(int nt, const Row* row, const P4* pts, int* otri, int* oadj) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < nt) {
-    I4 v = tri[t], a = adj[t];
+    I4 v = row[t].v, a = row[t].a;
     otri[3 * t] = (int)pts[v.x].id + 1; otri[3 * t + 1] = (int)pts[v.y].id + 1;
     otri[3 * t + 2] = (int)pts[v.z].id + 1;
     oadj[3 * t] = (a.x >> 2) + 1; oadj[3 * t + 1] = (a.y >> 2) + 1; oadj[3 * t + 2] = (a.z >> 2) + 1;

@@ -38,8 +38,7 @@ struct Density {   // same layout as fm_density in include/fishman_b200.h
 struct VdCtx {
   int n, n_tri;
   P4* pts;                    // generators, internal order (x,y,z updated in place by the Lloyd kernel)
-  const I4* tri;
-  const I4* adj;
+  const Row* row;             // triangle slots (dt_kernels.cuh)
   P4* cc;                     // circumcentres per triangle (w unused)
   double *cclon, *cclat;      // optional (may be null)
   const int* v2t;             // per vertex: some incident triangle
@@ -58,7 +57,7 @@ static const double kPi2 = 6.283185307179586476925287;
 // ------------------------------------------------------------ circumcentres
 struct KCircum {
   FM_HD static void run(const VdCtx& c, int t) {
-    I4 v = c.tri[t];
+    I4 v = c.row[t].v;
     const P4 &qa = c.pts[v.x], &qb = c.pts[v.y], &qc = c.pts[v.z];
     bool dg;
     P3 n = circumcentre(P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, P3{qc.x, qc.y, qc.z}, dg);
@@ -78,12 +77,12 @@ struct KCircum {
 // e+1 of that neighbour (e = the neighbour's edge index stored in adj).
 FM_HD inline int ring_start(const VdCtx& c, int i, int& k) {
   int t = c.v2t[i];
-  I4 v = c.tri[t];
+  I4 v = c.row[t].v;
   k = (v.x == i) ? 0 : ((v.y == i) ? 1 : 2);
   return t;
 }
 FM_HD inline int ring_next(const VdCtx& c, int t, int& k) {
-  int ne = geti(c.adj[t], (k + 1) % 3);
+  int ne = geti(c.row[t].a, (k + 1) % 3);
   k = ((ne & 3) + 1) % 3;
   return ne >> 2;
 }
@@ -105,7 +104,7 @@ struct KRingFill {
   FM_HD static void run(const VdCtx& c, int i) {
     int k, t0 = ring_start(c, i, k), t = t0, d = 0, best = 0x7fffffff, jbest = 0;
     do {
-      int nb = (int)c.pts[geti(c.tri[t], (k + 2) % 3)].id;
+      int nb = (int)c.pts[geti(c.row[t].v, (k + 2) % 3)].id;
       if (nb < best) { best = nb; jbest = d; }
       t = ring_next(c, t, k);
       d++;
@@ -115,7 +114,7 @@ struct KRingFill {
     for (int j = 0; j < d; j++) {
       int pos = off + (j - jbest + d) % d;
       c.ring_tri[pos] = t + 1;
-      c.ring_nbr[pos] = (int)c.pts[geti(c.tri[t], (k + 2) % 3)].id + 1;
+      c.ring_nbr[pos] = (int)c.pts[geti(c.row[t].v, (k + 2) % 3)].id + 1;
       t = ring_next(c, t, k);
     }
   }

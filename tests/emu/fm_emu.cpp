@@ -50,7 +50,7 @@ struct HostBackend {
   int fetch_orig(const DtCtx& c, int i) { return (int)c.pts[i].id; }
   void write_tris(const DtCtx& c, int t0, int cnt, const I4* tri, const I4* adj) {
     for (int i = 0; i < cnt; i++) {
-      c.tri[t0 + i] = tri[i]; c.adj[t0 + i] = adj[i];
+      c.row[t0 + i] = Row{tri[i], adj[i]};
       c.v2t[tri[i].x] = c.v2t[tri[i].y] = c.v2t[tri[i].z] = t0 + i;
     }
   }
@@ -87,7 +87,7 @@ extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_
   std::vector<P4> pts(n);
   for (int i = 0; i < n; i++) pts[i] = P4{xyz[3 * orig[i]], xyz[3 * orig[i] + 1], xyz[3 * orig[i] + 2], orig[i]};
   int T = 2 * n - 4;
-  std::vector<I4> tri(T), adj(T);
+  std::vector<Row> row(T);
   std::vector<int> loc(n, 0), rank(T + 1), flip_edge(T), role(T, 0), amark(T, 0), listA(T), listB(T), v2t(n, -1);
   std::vector<u64> winner(T), vote(T, kNone64), mailbox(3 * (size_t)T, 0);
   int counters[16] = {0}, err = 0;
@@ -95,7 +95,7 @@ extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_
   DtCtx c;
   memset(&c, 0, sizeof c);
   c.n = n; c.pts = pts.data(); c.v2t = v2t.data();
-  c.tri = tri.data(); c.adj = adj.data(); c.loc = loc.data(); c.winner = winner.data();
+  c.row = row.data(); c.loc = loc.data(); c.winner = winner.data();
   c.rank = rank.data(); c.vote = vote.data(); c.flip_edge = flip_edge.data(); c.role = role.data();
   c.mailbox = mailbox.data(); c.amark = amark.data(); c.counters = counters; c.err = &err; c.slow = slow.data();
   HostBackend be;
@@ -118,8 +118,8 @@ extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_
   if (c.n_tri != T) { snprintf(g_err, sizeof g_err, "triangle count %d != 2n-4", c.n_tri); return 1; }
   for (int t = 0; t < T; t++)
     for (int k = 0; k < 3; k++) {
-      tri_out[3 * t + k] = orig[geti(tri[t], k)] + 1;
-      adj_out[3 * t + k] = (geti(adj[t], k) >> 2) + 1;
+      tri_out[3 * t + k] = orig[geti(row[t].v, k)] + 1;
+      adj_out[3 * t + k] = (geti(row[t].a, k) >> 2) + 1;
     }
   if (stats) { stats[0] = st.rounds; stats[1] = st.subrounds; stats[2] = st.flips; stats[3] = st.max_active; }
   return 0;
