@@ -173,7 +173,9 @@ def workload_config(args):
     return {"workload": f"C4: {args.n}-generator uniform-density SCVT Lloyd loop (BASELINE.json configs[3]); "
                         "FIB lattice + 0.2h jitter, seed 0",
             "mode": args.mode, "density": "uniform", "generators": args.n,
-            "parallelism": f"replicated DT + sharded centroid x{args.gpus}" if args.gpus > 1 else "single GPU",
+            "parallelism": (f"replicated DT + sharded centroid x{args.gpus}, generator exchange: "
+                            + ("stores into peer memory over NVLink from the Lloyd kernel" if args.exchange == "p2p"
+                               else "NCCL all-gather")) if args.gpus > 1 else "single GPU",
             "l2": "working set (~0.6 GB of generators, triangles, adjacency, circumcentres) exceeds the 126 MB L2; no flush"}
 
 
@@ -201,7 +203,9 @@ def run_gpu(args):
     rho = fb.density_uniform()
     m = fb.Mesh.from_xyz(p, rank=rank, size=world)
     gather = None
-    if world > 1:
+    if world > 1 and args.exchange == "p2p":
+        m.peer_connect(dist)   # the Lloyd kernel stores into every rank's generator array over NVLink
+    elif world > 1:
         from fishman_b200 import sharding
         ptr, npad, beg, cnt = m.generator_block()
         assert (npad, beg, cnt) == sharding.block_bounds(n, rank, world)[:3]
@@ -218,7 +222,7 @@ def run_gpu(args):
         torch.cuda.synchronize()
 
     def device_steps(k):
-        if world == 1:
+        if gather is None:
             m.lloyd(rho, max_iter=k, tol=0.0, warm=warm)
         else:
             for _ in range(k):
@@ -240,7 +244,9 @@ def run_gpu(args):
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = clk.stop() if rank == 0 else None
     st = m.stats()
-    ms = wall_ms if world > 1 else ms_dev  # N > 1: NCCL runs on torch's stream, the barrier-bracketed span covers both
+    # NCCL exchange: the collective runs on torch's stream, so the barrier-bracketed span is the
+    # time; peer exchange: everything is on the handle's stream and its CUDA events see it all
+    ms = wall_ms if gather is not None else ms_dev
     if dist:
         t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -255,7 +261,7 @@ def run_gpu(args):
     t0 = time.perf_counter()
     for _ in range(args.steps):
         m.set_generators_soa(*hx)
-        if world == 1:
+        if gather is None:
             m.lloyd(rho, max_iter=1, tol=0.0, warm=warm)
         else:
             gather(m.lloyd_local(rho, warm=warm))
@@ -328,6 +334,8 @@ def main():
     ap.add_argument("--mode", default="warm", choices=["warm", "cold"])
     ap.add_argument("--n", type=int, default=N_C4)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: how the updated generator blocks reach the other ranks")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

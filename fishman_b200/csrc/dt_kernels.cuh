@@ -66,7 +66,7 @@ enum {
 };
 
 // error bits reported through DtCtx::err
-enum { FM_E_WALK = 1, FM_E_TOPOLOGY = 2, FM_E_OVERFLOW = 4 };
+enum { FM_E_WALK = 1, FM_E_TOPOLOGY = 2, FM_E_OVERFLOW = 4, FM_E_PEER = 8 };
 
 // Generator record: 32 bytes = one DRAM sector, so that a vertex gather costs one sector
 // instead of four (x, y, z, id in separate arrays) and ONE 256-bit load (LDG.E.ENL2.256 on

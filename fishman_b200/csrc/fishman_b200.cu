@@ -84,6 +84,13 @@ struct fm_handle {
   int *deg = nullptr, *ring_tri = nullptr, *ring_nbr = nullptr;
   int *ecount = nullptr, *de = nullptr, *ve_vvt = nullptr, *ve_vc = nullptr;
   double* stage = nullptr;  // 3n doubles: input-order staging of fm_get/set_generators
+  // peer exchange: `pts` and a PeerSync block live in one arena that is exported over CUDA IPC
+  // and mapped by the other ranks of the mesh (fm_peer_handle / fm_peer_attach)
+  char* arena = nullptr;
+  PeerSync* psync = nullptr;
+  void* peer_base[8] = {nullptr};
+  PeerCtx peer_ctx = {};
+  bool peers_attached = false;
   // the warm Lloyd iteration as a CUDA graph (reset, sweep, deferred sweep, flip loop, centroid,
   // readback copy): one launch call per iteration instead of seven
   cudaGraphExec_t warm_graph = nullptr;
@@ -183,6 +190,9 @@ struct fm_handle {
     if (rho) c.rho = *rho;
     c.cell_begin = blk_begin; c.cell_end = blk_begin + blk_count;
     c.maxdisp = (u64*)(counters + FM_C_MAXDISP); c.err = err;
+    if (peers_attached)
+      for (int k = 0; k < size; k++)
+        if (k != rank) c.peer_pts[c.n_peers++] = (P4*)peer_base[k];
     return c;
   }
 };
@@ -353,7 +363,13 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   A(cudaEventCreate(&h->ev0)); A(cudaEventCreate(&h->ev1));
   A(cudaMallocHost((void**)&h->pinned, 64 * sizeof(int)));
-  A(dalloc(&h->pts, h->n_pad));
+  {  // arena = generator records + PeerSync block (exported as one IPC allocation)
+    size_t pts_bytes = sizeof(P4) * (size_t)h->n_pad;
+    A(cudaMalloc((void**)&h->arena, pts_bytes + sizeof(PeerSync)));
+    h->pts = (P4*)h->arena;
+    h->psync = (PeerSync*)(h->arena + pts_bytes);
+    A(cudaMemsetAsync(h->psync, 0, sizeof(PeerSync), h->stream));
+  }
   A(dalloc(&h->orig, n)); A(dalloc(&h->inv, n)); A(dalloc(&h->v2t, n));
   A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n));
   A(dalloc(&h->rows, T)); A(dalloc(&h->cc, T));
@@ -453,7 +469,9 @@ extern "C" int fm_create_dist(int32_t n, const double* x, const double* y, const
 extern "C" void fm_destroy(fm_handle* h) {
   if (!h) return;
   if (h->stream) cudaStreamSynchronize(h->stream);
-  void* ptrs[] = {h->pts, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
+  for (int k = 0; k < 8; k++)
+    if (h->peer_base[k]) cudaIpcCloseMemHandle(h->peer_base[k]);
+  void* ptrs[] = {h->arena, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cc, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
@@ -493,10 +511,11 @@ static int readback(fm_handle* h, Readback* r, const char* where, bool enqueued 
   memcpy(&r->maxdisp, r->counters + FM_C_MAXDISP, sizeof(double));
   if (r->err) {
     cudaMemsetAsync(h->err, 0, sizeof(int), h->stream);
-    h->fail("%s: device reported error bits %d (%s%s%s)", where, r->err,
+    h->fail("%s: device reported error bits %d (%s%s%s%s)", where, r->err,
             (r->err & FM_E_WALK) ? "point walk did not terminate " : "",
             (r->err & FM_E_TOPOLOGY) ? "degenerate triangle / broken ring " : "",
-            (r->err & FM_E_OVERFLOW) ? "flip rounds did not terminate" : "");
+            (r->err & FM_E_OVERFLOW) ? "flip rounds did not terminate " : "",
+            (r->err & FM_E_PEER) ? "a peer rank did not reach the barrier" : "");
     return 1;
   }
   if (r->stamp > (1 << 27)) {  // stamps are about to run out: start over with clean words
@@ -711,7 +730,24 @@ extern "C" int fm_get_edges(fm_handle* h, int32_t* de, int32_t* ve_vvt, int32_t*
   return 0;
 }
 
+static void launch_peer_barrier(fm_handle* h, int phase) {
+  h->prof_begin();
+  fm_peer_barrier<<<1, 32, 0, h->stream>>>(h->peer_ctx, phase, h->counters);
+  h->note_cuda(cudaGetLastError(), "peer_barrier");
+  h->prof_end("peer_barrier", 0);
+}
+
+static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded);
+// Centroid stage of one iteration.  On a sharded mesh with attached peers the kernel runs
+// between two barriers: no rank overwrites generators another rank is still reading, and the
+// iteration ends when every block has arrived everywhere.
 static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded) {
+  if (h->peers_attached) launch_peer_barrier(h, 0);
+  launch_centroid_kernel(h, rho, guarded);
+  if (h->peers_attached) launch_peer_barrier(h, 1);
+}
+
+static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded) {
   Density d;
   d.kind = rho ? rho->kind : 0;
   if (rho) { d.cx = rho->cx; d.cy = rho->cy; d.cz = rho->cz; d.beta = rho->beta; d.alpha = rho->alpha; d.gamma = rho->gamma; }
@@ -776,7 +812,7 @@ static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
       }
     }
     if (h->warm_graph) {
-      h->n_launch += 4;  // sweep, deferred sweep, flip loop, centroid
+      h->n_launch += h->peers_attached ? 6 : 4;  // sweep, deferred sweep, flip loop, centroid (+ 2 barriers)
       cudaError_t e = cudaGraphLaunch(h->warm_graph, h->stream);
       if (e != cudaSuccess) { h->fail("cudaGraphLaunch: %s", cudaGetErrorString(e)); return 1; }
       return 0;
@@ -824,7 +860,10 @@ extern "C" int fm_lloyd_local(fm_handle* h, const fm_density* rho, int32_t warm,
 
 extern "C" int fm_lloyd(fm_handle* h, const fm_density* rho, int32_t max_iter, double tol, int32_t warm,
                         int32_t* iters, double* max_disp) {
-  if (h->size != 1) { h->fail("fm_lloyd on a sharded handle: use fm_lloyd_local + all-gather"); return 1; }
+  if (h->size != 1 && !h->peers_attached) {
+    h->fail("fm_lloyd on a sharded handle without peers: fm_peer_attach first, or use fm_lloyd_local + all-gather");
+    return 1;
+  }
   double md = 0.0;
   int it = 0;
   for (; it < max_iter;) {
@@ -834,6 +873,34 @@ extern "C" int fm_lloyd(fm_handle* h, const fm_density* rho, int32_t max_iter, d
   }
   if (iters) *iters = it;
   if (max_disp) *max_disp = md;
+  return 0;
+}
+
+// ---- peer exchange over NVLink (CUDA IPC between the processes of one box)
+extern "C" int fm_peer_handle(fm_handle* h, void* out64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  cudaIpcMemHandle_t hd;
+  FM_CUDA(cudaIpcGetMemHandle(&hd, h->arena));
+  memcpy(out64, &hd, sizeof hd);
+  return 0;
+}
+extern "C" int fm_peer_attach(fm_handle* h, const void* handles) {
+  if (h->size < 2 || h->size > 8) { h->fail("fm_peer_attach: size must be 2..8, got %d", h->size); return 1; }
+  if (h->peers_attached) { h->fail("fm_peer_attach: already attached"); return 1; }
+  FM_CUDA(h->sync());
+  size_t pts_bytes = sizeof(P4) * (size_t)h->n_pad;
+  PeerCtx pc = {};
+  pc.rank = h->rank; pc.size = h->size;
+  for (int k = 0; k < h->size; k++) {
+    if (k == h->rank) { pc.sync[k] = h->psync; continue; }
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, (const char*)handles + 64 * (size_t)k, sizeof hd);
+    FM_CUDA(cudaIpcOpenMemHandle(&h->peer_base[k], hd, cudaIpcMemLazyEnablePeerAccess));
+    pc.sync[k] = (PeerSync*)((char*)h->peer_base[k] + pts_bytes);
+  }
+  h->peer_ctx = pc;
+  h->peers_attached = true;
+  if (h->warm_graph) { cudaGraphExecDestroy(h->warm_graph); h->warm_graph = nullptr; }
   return 0;
 }
 

@@ -124,6 +124,56 @@ __global__ void __launch_bounds__(128, FM_OCC_CENTROID) fm_centroid_update(const
   }
 }
 
+// ---- peer exchange over NVLink (fm_peer_attach): barrier between the ranks of a sharded mesh
+// One PeerSync block per rank, inside the IPC-exported arena, mapped by every peer.
+//   flag[k]      written by rank k: the last barrier epoch rank k has reached
+//   epoch        local: barriers executed so far (every rank executes the same sequence)
+//   maxdisp_all  bits of the largest chord displacement over ALL ranks of the current iteration
+struct PeerSync {
+  int flag[8];
+  int epoch;
+  int pad[7];
+  u64 maxdisp_all;
+  u64 pad2[7];
+};
+struct PeerCtx {
+  PeerSync* sync[8];  // by rank; sync[rank] is the local block
+  int rank, size;
+};
+// phase 0 (before the centroid kernel: every rank has finished reading the generators) and
+// phase 1 (after it: every rank's stores into this rank's generator array have landed, and the
+// displacement maxima have been combined).  One warp; lane k talks to rank k.  A rank that does
+// not show up within ~2 s of SM clocks sets FM_E_PEER instead of hanging the device.
+__global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
+  __shared__ int ep;
+  const int k = threadIdx.x;
+  PeerSync* self = pc.sync[pc.rank];
+  if (k == 0) {
+    ep = self->epoch + 1;
+    self->epoch = ep;
+    if (phase == 0) self->maxdisp_all = 0;
+  }
+  __syncthreads();
+  const int e = ep;
+  if (k < pc.size) {
+    if (phase == 1) {
+      u64 mine = *(volatile u64*)(counters + FM_C_MAXDISP);
+      atomicMax_system((unsigned long long*)&pc.sync[k]->maxdisp_all, (unsigned long long)mine);
+    }
+    __threadfence_system();
+    *(volatile int*)&pc.sync[k]->flag[pc.rank] = e;
+    long long t0 = clock64();
+    while (*(volatile int*)&self->flag[k] < e) {
+      if (clock64() - t0 > 4000000000LL) { atomicOr(counters + FM_C_ERR, FM_E_PEER); break; }
+    }
+  }
+  __syncthreads();
+  if (phase == 1 && k == 0) {
+    __threadfence_system();
+    *(volatile u64*)(counters + FM_C_MAXDISP) = *(volatile u64*)&self->maxdisp_all;
+  }
+}
+
 // ---- spatial renumbering of the triangle slots (after a cold build)
 // Slots are handed out in creation order, so neighbours on the sphere end up far apart in
 // memory.  Sorting the slots by their smallest vertex index (vertices are in Morton order)

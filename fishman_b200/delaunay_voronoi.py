@@ -190,6 +190,17 @@ class Mesh:
         self._chk(_lib.lib().fm_generator_block(self._h, C.byref(p), C.byref(npad), C.byref(beg), C.byref(cnt)))
         return p.value, npad.value, beg.value, cnt.value
 
+    def peer_connect(self, dist):
+        """Maps the generator arrays of all ranks into each other (fm_peer_handle /
+        fm_peer_attach); `dist` is an initialised torch.distributed, used only to pass the
+        64-byte IPC handles around.  Afterwards lloyd() runs on the sharded mesh."""
+        buf = C.create_string_buffer(64)
+        self._chk(_lib.lib().fm_peer_handle(self._h, buf))
+        got = [None] * self.size
+        dist.all_gather_object(got, buf.raw)
+        self._chk(_lib.lib().fm_peer_attach(self._h, b"".join(got)))
+        dist.barrier()
+
     # ---- measurement
     def timer_begin(self):
         self._chk(_lib.lib().fm_timer_begin(self._h))

@@ -20,7 +20,7 @@ module fishman_gpu_c
   public :: fm_create, fm_create_lonlat, fm_create_dist, fm_destroy, fm_last_error
   public :: fm_triangulate, fm_retriangulate, fm_counts, fm_get_triangles
   public :: fm_voronoi, fm_get_circumcentres, fm_get_rings, fm_get_edges
-  public :: fm_lloyd, fm_lloyd_local, fm_generator_block
+  public :: fm_lloyd, fm_lloyd_local, fm_generator_block, fm_peer_handle, fm_peer_attach
   public :: fm_get_generators, fm_set_generators
   public :: fm_error_message
 
@@ -142,6 +142,19 @@ module fishman_gpu_c
       type(c_ptr), intent(out) :: d_records
       integer(c_int64_t), intent(out) :: n_padded, begin, count
     end function fm_generator_block
+
+    ! 64-byte CUDA IPC handle of this rank; exchange with MPI_Allgather, then attach all of them
+    integer(c_int) function fm_peer_handle(h, out64) bind(C, name='fm_peer_handle')
+      import :: c_int, c_char, c_ptr
+      type(c_ptr), value :: h
+      character(kind=c_char), intent(out) :: out64(64)
+    end function fm_peer_handle
+
+    integer(c_int) function fm_peer_attach(h, handles) bind(C, name='fm_peer_attach')
+      import :: c_int, c_char, c_ptr
+      type(c_ptr), value :: h
+      character(kind=c_char), intent(in) :: handles(*)
+    end function fm_peer_attach
 
     integer(c_int) function fm_get_generators(h, x, y, z) bind(C, name='fm_get_generators')
       import :: c_int, c_double, c_ptr

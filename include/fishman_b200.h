@@ -98,6 +98,15 @@ int fm_lloyd_local(fm_handle* h, const fm_density* rho, int32_t warm, double* ma
  * block is records [begin, begin + count).  One in-place all-gather of count records per rank
  * completes an iteration. */
 int fm_generator_block(fm_handle* h, void** d_records, int64_t* n_padded, int64_t* begin, int64_t* count);
+/* Peer exchange over NVLink (sharded handles, one process per GPU of one box): instead of a
+ * collective after the Lloyd kernel, the kernel itself stores every updated generator into the
+ * generator arrays of all ranks through CUDA IPC peer mappings, between two device-side barriers.
+ * fm_peer_handle writes this rank's 64-byte IPC handle; the host exchanges the handles by
+ * whatever means it has (MPI_Allgather, torch.distributed) and passes all `size` of them, in
+ * rank order, to fm_peer_attach.  Afterwards fm_lloyd runs the whole loop on a sharded handle
+ * (every rank calls it with the same arguments) and *max_disp is the maximum over all ranks. */
+int fm_peer_handle(fm_handle* h, void* out64);
+int fm_peer_attach(fm_handle* h, const void* handles);
 /* generators in input order (device -> host) */
 int fm_get_generators(fm_handle* h, double* x, double* y, double* z);
 /* replace the generators (host -> device), keeping the internal order and topology */

@@ -1,0 +1,65 @@
+"""Multi-GPU consistency check, run under torchrun (one process per GPU):
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+      --master-port 29511 tools/dist_check.py [n] [iters]
+
+Every rank builds (a) a sharded mesh whose Lloyd kernel stores the updated generators into all
+ranks' arrays over NVLink (fm_peer_attach), (b) a sharded mesh exchanged by an NCCL all-gather,
+(c) an unsharded mesh on its own GPU, runs `iters` Lloyd iterations on each and requires the
+three generator sets to be bit-identical on every rank, and the displacement maxima equal.
+Prints one line per rank; exit code 0 = all equal."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import fishman_b200 as fb  # noqa: E402
+from fishman_b200 import points, sharding  # noqa: E402
+
+
+def main():
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 163842
+    iters = int(sys.argv[2]) if len(sys.argv) > 2 else 10
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    p = points.fibonacci(n, seed=0, jitter=0.2)
+    rho = fb.density_x4() if os.environ.get("FM_CHECK_DENSITY") == "x4" else fb.density_uniform()
+
+    ref = fb.Mesh.from_xyz(p)
+    md_ref = [ref.lloyd(rho, max_iter=1, warm=True)[1] for _ in range(iters)]
+    g_ref = ref.generators()
+    ref.close()
+
+    a = fb.Mesh.from_xyz(p, rank=rank, size=world)
+    a.peer_connect(dist)
+    md_a = [a.lloyd(rho, max_iter=1, warm=True)[1] for _ in range(iters)]
+    g_a = a.generators()
+    a.close()
+
+    b = fb.Mesh.from_xyz(p, rank=rank, size=world)
+    ptr, npad, beg, cnt = b.generator_block()
+    full = sharding.DeviceRecords(ptr, npad, f"cuda:{local}").tensor
+    md_b = []
+    for _ in range(iters):
+        md = b.lloyd_local(rho, warm=True)
+        sharding.allgather_blocks(dist, full, beg, cnt)
+        md_b.append(sharding.reduce_max(dist, md, f"cuda:{local}"))
+    g_b = b.generators()
+    b.close()
+
+    ok = (np.array_equal(g_ref, g_a) and np.array_equal(g_ref, g_b) and md_ref == md_a and md_ref == md_b)
+    print(f"rank {rank}/{world}: n={n} iters={iters} p2p==single {np.array_equal(g_ref, g_a)} "
+          f"nccl==single {np.array_equal(g_ref, g_b)} maxdisp equal {md_ref == md_a and md_ref == md_b} "
+          f"last maxdisp {md_ref[-1]:.3e}", flush=True)
+    t = torch.tensor([0 if ok else 1], device=f"cuda:{local}")
+    dist.all_reduce(t)
+    dist.destroy_process_group()
+    sys.exit(0 if int(t.item()) == 0 else 1)
+
+
+if __name__ == "__main__":
+    main()
