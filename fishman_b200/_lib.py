@@ -11,7 +11,8 @@ _lib = None
 SYMBOLS = [
     "fm_create", "fm_create_lonlat", "fm_create_dist", "fm_destroy", "fm_last_error", "fm_triangulate", "fm_retriangulate",
     "fm_counts", "fm_get_triangles", "fm_voronoi", "fm_get_circumcentres", "fm_get_rings",
-    "fm_get_edges", "fm_lloyd", "fm_lloyd_local", "fm_generator_block", "fm_peer_handle", "fm_peer_attach", "fm_get_generators",
+    "fm_get_edges", "fm_mpas", "fm_get_mpas_edges", "fm_get_mpas_cells", "fm_get_mpas_vertices",
+    "fm_get_mpas_edges_on_edge", "fm_lloyd", "fm_lloyd_local", "fm_generator_block", "fm_peer_handle", "fm_peer_attach", "fm_get_generators",
     "fm_set_generators", "fm_host_alloc", "fm_host_free", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
     "fm_profile_enable", "fm_profile_get", "fm_device_info",
 ]
@@ -48,6 +49,11 @@ def lib():
     L.fm_get_circumcentres.argtypes = [vp, dp, dp]
     L.fm_get_rings.argtypes = [vp, ip, ip, ip]
     L.fm_get_edges.argtypes = [vp, ip, ip, ip]
+    L.fm_mpas.argtypes = [vp, i32, ip]
+    L.fm_get_mpas_edges.argtypes = [vp, dp, dp, dp, dp, dp, dp, dp]
+    L.fm_get_mpas_cells.argtypes = [vp, ip, dp, dp]
+    L.fm_get_mpas_vertices.argtypes = [vp, ip, ip, dp, dp]
+    L.fm_get_mpas_edges_on_edge.argtypes = [vp, ip, ip, dp]
     L.fm_lloyd.argtypes = [vp, C.POINTER(Density), i32, C.c_double, i32, ip, dp]
     L.fm_lloyd_local.argtypes = [vp, C.POINTER(Density), i32, dp]
     L.fm_generator_block.argtypes = [vp, C.POINTER(vp), i64p, i64p, i64p]

@@ -10,6 +10,7 @@
 
 #include "../../include/fishman_b200.h"
 #include "launch_kernels.cuh"
+#include "mpas_kernels.cuh"
 
 using namespace fm;
 
@@ -84,6 +85,15 @@ struct fm_handle {
   int *deg = nullptr, *ring_tri = nullptr, *ring_nbr = nullptr;
   int *ecount = nullptr, *de = nullptr, *ve_vvt = nullptr, *ve_vc = nullptr;
   double* stage = nullptr;  // 3n doubles: input-order staging of fm_get/set_generators
+  // MPAS adapter arrays (fm_mpas), allocated on first use
+  struct Mpas {
+    int max_edges = 0, cap_max_edges = 0;
+    int *ring_edge = nullptr, *cells_on_vertex = nullptr, *edges_on_vertex = nullptr, *n_eoe = nullptr, *eoe = nullptr;
+    double *xyz_edge = nullptr, *lonlat_edge = nullptr, *edge5 = nullptr;  // edge5: dv, dc, dv1, dv2, angle (5 x E)
+    double *area_cell = nullptr, *area_tri = nullptr, *kite_ring = nullptr, *kite_vtx = nullptr, *weights = nullptr;
+    double* sums = nullptr;
+    bool have = false;
+  } mp;
   // peer exchange: `pts` and a PeerSync block live in one arena that is exported over CUDA IPC
   // and mapped by the other ranks of the mesh (fm_peer_handle / fm_peer_attach)
   char* arena = nullptr;
@@ -471,6 +481,13 @@ extern "C" void fm_destroy(fm_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   for (int k = 0; k < 8; k++)
     if (h->peer_base[k]) cudaIpcCloseMemHandle(h->peer_base[k]);
+  {
+    auto& m = h->mp;
+    void* mptrs[] = {m.ring_edge, m.cells_on_vertex, m.edges_on_vertex, m.n_eoe, m.eoe, m.xyz_edge, m.lonlat_edge,
+                     m.edge5, m.area_cell, m.area_tri, m.kite_ring, m.kite_vtx, m.weights, m.sums};
+    for (void* p : mptrs)
+      if (p) cudaFree(p);
+  }
   void* ptrs[] = {h->arena, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cc, h->cclon, h->cclat,
@@ -580,7 +597,7 @@ static int triangulate_cold(fm_handle* h) {
   if (readback(h, &r, "delaunay_triangulation")) return 1;
   account(h, r, st.rounds);
   h->n_cold++;
-  h->have_dt = true; h->have_cc = false; h->have_vd = false; h->have_edges = false;
+  h->have_dt = true; h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
   return 0;
 }
 
@@ -613,7 +630,7 @@ static int triangulate(fm_handle* h, bool warm, const char* where) {
     if (r.counters[3] == 0) {
       account(h, r, 0);
       h->n_warm++;
-      h->have_cc = true; h->have_vd = false; h->have_edges = false;
+      h->have_cc = true; h->have_vd = false; h->have_edges = false; h->mp.have = false;
       return 0;
     }
   }
@@ -730,6 +747,113 @@ extern "C" int fm_get_edges(fm_handle* h, int32_t* de, int32_t* ve_vvt, int32_t*
   return 0;
 }
 
+// ---- MPAS adapter arithmetic on the device: mpas_mesh_adapt MM:181-345 and
+// calc_weightsOnEdge MM:442-561 over the ring / edge tables of fm_voronoi(h, 1)
+extern "C" int fm_mpas(fm_handle* h, int32_t strict, int32_t* max_edges) {
+  if (!h->have_edges) { h->fail("fm_mpas needs fm_voronoi(h, 1) (mpas_mesh_output after voronoi_diagram(all=.true.))"); return 1; }
+  auto& m = h->mp;
+  size_t n = (size_t)h->n, T = (size_t)h->n_tri, E = 3 * n - 6;
+  if (!m.ring_edge) {
+    FM_CUDA(dalloc(&m.ring_edge, 3 * T)); FM_CUDA(dalloc(&m.cells_on_vertex, 3 * T)); FM_CUDA(dalloc(&m.edges_on_vertex, 3 * T));
+    FM_CUDA(dalloc(&m.n_eoe, E)); FM_CUDA(dalloc(&m.xyz_edge, 3 * E)); FM_CUDA(dalloc(&m.lonlat_edge, 2 * E));
+    FM_CUDA(dalloc(&m.edge5, 5 * E)); FM_CUDA(dalloc(&m.area_cell, n)); FM_CUDA(dalloc(&m.area_tri, T));
+    FM_CUDA(dalloc(&m.kite_ring, 3 * T)); FM_CUDA(dalloc(&m.kite_vtx, 3 * T)); FM_CUDA(dalloc(&m.sums, 4));
+  }
+  MpasCtx c;
+  memset(&c, 0, sizeof c);
+  c.n = h->n; c.n_tri = h->n_tri; c.n_edge = (int)E;
+  c.pts = h->pts; c.inv = h->inv; c.row = h->rows; c.cc = h->cc;
+  c.off = h->deg; c.ring_tri = h->ring_tri; c.ring_nbr = h->ring_nbr; c.eoff = h->ecount;
+  c.de = h->de; c.ve_vvt = h->ve_vvt;
+  c.ring_edge = m.ring_edge; c.xyz_edge = m.xyz_edge; c.lonlat_edge = m.lonlat_edge;
+  c.dv = m.edge5; c.dc = m.edge5 + E; c.dv1 = m.edge5 + 2 * E; c.dv2 = m.edge5 + 3 * E; c.angle = m.edge5 + 4 * E;
+  c.area_cell = m.area_cell; c.area_tri = m.area_tri; c.kite_ring = m.kite_ring; c.kite_vtx = m.kite_vtx;
+  c.cells_on_vertex = m.cells_on_vertex; c.edges_on_vertex = m.edges_on_vertex; c.n_eoe = m.n_eoe;
+  c.sums = m.sums; c.maxdeg = h->counters + 7; c.err = h->err;
+  FM_CUDA(cudaMemsetAsync(m.sums, 0, 4 * sizeof(double), h->stream));
+  FM_CUDA(cudaMemsetAsync(h->counters + 7, 0, sizeof(int), h->stream));
+  const int B = 128;
+  auto nb = [&](size_t cnt) { return (unsigned)((cnt + B - 1) / B); };
+  h->prof_begin(); fm_mpas_ring_edge<<<nb(n), B, 0, h->stream>>>(c); h->prof_end("mpas_ring_edge", n);
+  h->prof_begin(); fm_mpas_edges<<<nb(E), B, 0, h->stream>>>(c); h->prof_end("mpas_edges", E);
+  h->prof_begin(); fm_mpas_cells<<<nb(n), B, 0, h->stream>>>(c); h->prof_end("mpas_cells", n);
+  h->prof_begin(); fm_mpas_vertices<<<nb(T), B, 0, h->stream>>>(c); h->prof_end("mpas_vertices", T);
+  Readback r;
+  if (readback(h, &r, "fm_mpas")) return 1;
+  int me = r.counters[7];
+  if (me < 3 || me > 4096) { h->fail("fm_mpas: bad largest cell degree %d", me); return 1; }
+  if (me > m.cap_max_edges) {
+    if (m.eoe) { cudaFree(m.eoe); cudaFree(m.weights); m.eoe = nullptr; m.weights = nullptr; }
+    FM_CUDA(dalloc(&m.eoe, 2 * (size_t)me * E)); FM_CUDA(dalloc(&m.weights, 2 * (size_t)me * E));
+    m.cap_max_edges = me;
+  }
+  m.max_edges = me;
+  c.max_edges = me; c.eoe = m.eoe; c.weights = m.weights;
+  h->prof_begin(); fm_mpas_weights<<<nb(E), B, 0, h->stream>>>(c); h->prof_end("mpas_weights", E);
+  double sums[4];
+  FM_CUDA(cudaMemcpyAsync(sums, m.sums, sizeof sums, cudaMemcpyDeviceToHost, h->stream));
+  if (readback(h, &r, "fm_mpas")) return 1;
+  if (max_edges) *max_edges = me;
+  if (strict) {  // the reference's fatal checks: MM:306, MM:320, MM:339, MM:469-475
+    const double four_pi = 4.0 * 3.14159265358979323846;
+    const char* what = nullptr;
+    if (fabs(sums[0] - four_pi) > 1.0e-10) what = "Too large total cell area error!";
+    else if (fabs(sums[1] - four_pi) > 1.0e-10) what = "Too large total triangle area error!";
+    else if (fabs(sums[2] - four_pi) > 1.0e-10) what = "Too large total kite area error!";
+    else if (sums[3] > 1.0e-10) what = "Internal error! (kite fractions of a cell do not sum to 1)";
+    if (what) { h->fail("%s", what); return 1; }
+  }
+  m.have = true;
+  return 0;
+}
+
+template <class T>
+static int d2h(fm_handle* h, T* dst, const T* src, size_t cnt) {
+  if (dst) FM_CUDA(cudaMemcpyAsync(dst, src, sizeof(T) * cnt, cudaMemcpyDeviceToHost, h->stream));
+  return 0;
+}
+#define FM_NEED_MPAS(name) if (!h->mp.have) { h->fail(name " before fm_mpas"); return 1; }
+extern "C" int fm_get_mpas_edges(fm_handle* h, double* xyz, double* lonlat, double* dv, double* dc, double* dv1,
+                                 double* dv2, double* angle) {
+  FM_NEED_MPAS("fm_get_mpas_edges");
+  size_t E = 3 * (size_t)h->n - 6;
+  auto& m = h->mp;
+  if (d2h(h, xyz, m.xyz_edge, 3 * E) || d2h(h, lonlat, m.lonlat_edge, 2 * E) || d2h(h, dv, m.edge5, E) ||
+      d2h(h, dc, m.edge5 + E, E) || d2h(h, dv1, m.edge5 + 2 * E, E) || d2h(h, dv2, m.edge5 + 3 * E, E) ||
+      d2h(h, angle, m.edge5 + 4 * E, E)) return 1;
+  FM_CUDA(h->sync());
+  return 0;
+}
+extern "C" int fm_get_mpas_cells(fm_handle* h, int32_t* edges_on_cell, double* area_cell, double* kite_on_cell) {
+  FM_NEED_MPAS("fm_get_mpas_cells");
+  auto& m = h->mp;
+  size_t tot = 3 * (size_t)h->n_tri;
+  if (d2h(h, edges_on_cell, m.ring_edge, tot) || d2h(h, area_cell, m.area_cell, (size_t)h->n) ||
+      d2h(h, kite_on_cell, m.kite_ring, tot)) return 1;
+  FM_CUDA(h->sync());
+  return 0;
+}
+extern "C" int fm_get_mpas_vertices(fm_handle* h, int32_t* cells_on_vertex, int32_t* edges_on_vertex,
+                                    double* area_triangle, double* kite_areas_on_vertex) {
+  FM_NEED_MPAS("fm_get_mpas_vertices");
+  auto& m = h->mp;
+  size_t T = (size_t)h->n_tri;
+  if (d2h(h, cells_on_vertex, m.cells_on_vertex, 3 * T) || d2h(h, edges_on_vertex, m.edges_on_vertex, 3 * T) ||
+      d2h(h, area_triangle, m.area_tri, T) || d2h(h, kite_areas_on_vertex, m.kite_vtx, 3 * T)) return 1;
+  FM_CUDA(h->sync());
+  return 0;
+}
+extern "C" int fm_get_mpas_edges_on_edge(fm_handle* h, int32_t* n_edges_on_edge, int32_t* edges_on_edge,
+                                         double* weights_on_edge) {
+  FM_NEED_MPAS("fm_get_mpas_edges_on_edge");
+  auto& m = h->mp;
+  size_t E = 3 * (size_t)h->n - 6, row = 2 * (size_t)m.max_edges;
+  if (d2h(h, n_edges_on_edge, m.n_eoe, E) || d2h(h, edges_on_edge, m.eoe, row * E) ||
+      d2h(h, weights_on_edge, m.weights, row * E)) return 1;
+  FM_CUDA(h->sync());
+  return 0;
+}
+
 static void launch_peer_barrier(fm_handle* h, int phase) {
   h->prof_begin();
   fm_peer_barrier<<<1, 32, 0, h->stream>>>(h->peer_ctx, phase, h->counters);
@@ -836,7 +960,7 @@ static int lloyd_iteration(fm_handle* h, const fm_density* rho, int warm, double
     if (r.counters[3] == 0) {
       account(h, r, 0);
       h->n_warm++;
-      h->have_cc = false; h->have_vd = false; h->have_edges = false;
+      h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
       *maxdisp = r.maxdisp;
       return 0;
     }
@@ -846,7 +970,7 @@ static int lloyd_iteration(fm_handle* h, const fm_density* rho, int warm, double
   if (circumcentres(h, false)) return 1;
   launch_centroid(h, rho, false);
   if (readback(h, &r, "fm_lloyd")) return 1;
-  h->have_cc = false; h->have_vd = false; h->have_edges = false;
+  h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
   *maxdisp = r.maxdisp;
   return h->cuda_failed ? 1 : 0;
 }
@@ -926,7 +1050,7 @@ static int xfer_generators(fm_handle* h, double* x, double* y, double* z, bool t
     FM_CUDA(cudaMemcpyAsync(iy, y, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     FM_CUDA(cudaMemcpyAsync(iz, z, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     fm_gather_sorted<<<nb, 256, 0, h->stream>>>(n, h->orig, ix, iy, iz, h->pts, h->inv);
-    h->have_cc = false; h->have_vd = false; h->have_edges = false;
+    h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
   }
   h->n_launch++;
   FM_CUDA(h->sync());

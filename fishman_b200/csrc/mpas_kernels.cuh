@@ -1,0 +1,244 @@
+// mpas_kernels.cuh -- the arithmetic of the MPAS adapter on the device:
+// mpas_mesh_adapt (/root/reference/src/mpas_mesh_mod.F90:181-345, "MM") and calc_weightsOnEdge
+// (MM:442-561), with the geometry helpers of /root/reference/src/sphere_geometry_mod.F90 ("SG"):
+// intersect SG:316-363, calc_arc_length SG:289-314, calc_sphere_angle SG:247-285, calc_area
+// SG:198-227.  The reference walks its container graph serially; here every edge, cell and
+// Voronoi vertex is one thread over the flat ring / edge tables fm_voronoi(all) left on the
+// device.  CPU restatement: oracle/fishman_oracle.c fo_mpas.
+//
+// Index conventions (those the reference reaches after its order fix-ups, DV:462-582):
+//   ring position j of a cell <-> verticesOnCell(j), cellsOnCell(j), edgesOnCell(j); edge j runs
+//   from vertex j to vertex j+1 with the cell on its left and is the edge to cellsOnCell(j);
+//   around a Voronoi vertex: counter-clockwise, cellsOnVertex(k) on the left of edgesOnVertex(k)
+//   seen from the vertex, starting at the vertex's lowest edge id (DV:454-455).
+#pragma once
+#include "vd_kernels.cuh"
+
+namespace fm {
+
+struct MpasCtx {
+  int n, n_tri, n_edge, max_edges;
+  const P4* pts;       // generators, internal order; .id = original id
+  const int* inv;      // original id -> internal index
+  const Row* row;      // triangle slots (vertex ids internal)
+  const P4* cc;        // circumcentres
+  const int* off;      // per ORIGINAL cell id: ring offsets (n + 1)
+  const int *ring_tri, *ring_nbr;  // 1-based
+  const int* eoff;     // per original cell id: first edge it creates (n + 1)
+  const int *de, *ve_vvt;          // 2 x E, 1-based
+  int* ring_edge;      // per ring position: 1-based edge id (edgesOnCell)
+  double* xyz_edge;    // 3 x E
+  double* lonlat_edge; // 2 x E
+  double *dv, *dc, *dv1, *dv2, *angle;
+  double *area_cell, *area_tri, *kite_ring, *kite_vtx;
+  int *cells_on_vertex, *edges_on_vertex;  // 3 x T
+  int* n_eoe;          // E
+  int* eoe;            // 2 max_edges x E
+  double* weights;     // 2 max_edges x E
+  double* sums;        // [0] cells, [1] triangles, [2] kites, [3] max |sum R - 1|
+  int* maxdeg;
+  int* err;
+};
+
+static const double kPi = 3.14159265358979323846;
+
+__device__ __forceinline__ P3 m_cross(const P3& a, const P3& b) {
+  return P3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+__device__ __forceinline__ double m_dot(const P3& a, const P3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ P3 m_norm(const P3& v) {  // norm_vector, SG:229-243
+  double n = sqrt(m_dot(v, v));
+  return n != 0.0 ? P3{v.x / n, v.y / n, v.z / n} : v;
+}
+__device__ __forceinline__ double m_arc(const P3& a, const P3& b) {  // SG:289-296
+  return acos(fmax(fmin(m_dot(a, b), 1.0), -1.0));
+}
+__device__ __forceinline__ double m_angle(const P3& a, const P3& b, const P3& c) {  // SG:247-263
+  P3 nab = m_norm(m_cross(a, b)), nbc = m_norm(m_cross(b, c));
+  double res = acos(-fmax(fmin(m_dot(nab, nbc), 1.0), -1.0));
+  if (m_dot(m_cross(nab, nbc), a) < 0.0) res = kPi2 - res;
+  return res;
+}
+__device__ __forceinline__ P3 m_lonlat_xyz(double lon, double lat) {  // cartesian_transform, SG:76-85
+  double cl = cos(lat);
+  return P3{cl * cos(lon), cl * sin(lon), sin(lat)};
+}
+__device__ __forceinline__ P3 m_p3(const P4& q) { return P3{q.x, q.y, q.z}; }
+__device__ __forceinline__ P3 m_edge_point(const MpasCtx& c, int e1) {  // e1: 1-based edge id
+  const double* p = c.xyz_edge + 3 * (size_t)(e1 - 1);
+  return P3{p[0], p[1], p[2]};
+}
+
+// edgesOnCell: the edge at ring position j of cell i is created by the cell with the smaller id
+// at ITS ring position (DV:413-460), numbered eoff[creator] + (earlier positions that create one)
+__device__ __forceinline__ int m_created_edge(const MpasCtx& c, int cell, int other) {
+  int b = c.off[cell], d = c.off[cell + 1] - b, k = 0;
+  for (int q = 0; q < d; q++) {
+    int nb = c.ring_nbr[b + q] - 1;
+    if (nb == other) return c.eoff[cell] + k + 1;
+    k += (nb > cell);
+  }
+  return 0;
+}
+__global__ void fm_mpas_ring_edge(MpasCtx c) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= c.n) return;
+  int b = c.off[i], d = c.off[i + 1] - b;
+  atomicMax(c.maxdeg, d);
+  for (int j = 0; j < d; j++) {
+    int nb = c.ring_nbr[b + j] - 1;
+    int e = nb > i ? m_created_edge(c, i, nb) : m_created_edge(c, nb, i);
+    if (e == 0) atomicOr(c.err, FM_E_TOPOLOGY);
+    c.ring_edge[b + j] = e;
+  }
+}
+
+// per edge: xEdge.. (intersect, SG:316-363), dvEdge, dcEdge, dv1Edge, dv2Edge, angleEdge (MM:244-266)
+__global__ void fm_mpas_edges(MpasCtx c) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= c.n_edge) return;
+  int c1 = c.de[2 * e] - 1, c2 = c.de[2 * e + 1] - 1;
+  int v1 = c.ve_vvt[2 * e] - 1, v2 = c.ve_vvt[2 * e + 1] - 1;
+  P3 A = m_p3(c.pts[c.inv[c1]]), B = m_p3(c.pts[c.inv[c2]]), C = m_p3(c.cc[v1]), D = m_p3(c.cc[v2]);
+  P3 v = m_cross(m_cross(A, B), m_cross(C, D));
+  double r = sqrt(m_dot(v, v));
+  if (!(r > kEps)) { atomicOr(c.err, FM_E_TOPOLOGY); return; }  // "Unable to find intersection between DE and VE!"
+  v = P3{v.x / r, v.y / r, v.z / r};
+  double lat1 = asin(v.z), lat2 = -lat1, lon1 = atan2(v.y, v.x), lon2 = lon1 - kPi;
+  if (lon1 < 0.0) lon1 += kPi2;
+  if (lon1 > kPi2) lon1 -= kPi2;
+  if (lon2 < 0.0) lon2 += kPi2;
+  if (lon2 > kPi2) lon2 -= kPi2;
+  double lon = lon1, lat = lat1;
+  P3 X = m_lonlat_xyz(lon1, lat1);
+  if (m_dot(m_cross(A, X), m_cross(B, X)) >= 0 || m_dot(m_cross(C, X), m_cross(D, X)) >= 0) {
+    lon = lon2; lat = lat2;
+    X = m_lonlat_xyz(lon2, lat2);
+  }
+  c.xyz_edge[3 * (size_t)e] = X.x; c.xyz_edge[3 * (size_t)e + 1] = X.y; c.xyz_edge[3 * (size_t)e + 2] = X.z;
+  c.lonlat_edge[2 * (size_t)e] = lon; c.lonlat_edge[2 * (size_t)e + 1] = lat;
+  c.dv[e] = m_arc(C, D);
+  c.dc[e] = m_arc(A, B);
+  c.dv1[e] = m_arc(C, X);
+  c.dv2[e] = m_arc(D, X);
+  double alon = atan2(A.y, A.x);                 // DVT1%lon, %lat (inverse_cartesian_transform, SG:112-121)
+  if (alon < 0.0) alon += kPi2;
+  double xlon = alon + 0.1 * kPi;                // MM:262-266
+  if (xlon > kPi2) xlon -= kPi2;
+  c.angle[e] = m_angle(m_lonlat_xyz(xlon, asin(A.z)), A, B);
+}
+
+__device__ __forceinline__ void m_block_add(double v, double* dst) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0 && v != 0.0) atomicAdd(dst, v);
+}
+
+// per cell: areaCell (MM:296-308) and its kites in ring order (MM:324-341):
+// kite(j) = area(xEdge(edge j), cell, xEdge(edge j-1), vertex j)
+__global__ void fm_mpas_cells(MpasCtx c) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double area = 0.0, ksum = 0.0;
+  if (i < c.n) {
+    int b = c.off[i], d = c.off[i + 1] - b;
+    P3 g = m_p3(c.pts[c.inv[i]]);
+    P3 pm = m_p3(c.cc[c.ring_tri[b + d - 1] - 1]), p0 = m_p3(c.cc[c.ring_tri[b] - 1]);
+    P3 em = m_edge_point(c, c.ring_edge[b + d - 1]);
+    for (int j = 0; j < d; j++) {
+      int jn = (j + 1 == d) ? 0 : j + 1;
+      P3 pn = m_p3(c.cc[c.ring_tri[b + jn] - 1]);
+      area += m_angle(pm, p0, pn);                                  // calc_area, SG:198-227
+      P3 ej = m_edge_point(c, c.ring_edge[b + j]);
+      double k = m_angle(p0, ej, g) + m_angle(ej, g, em) + m_angle(g, em, p0) + m_angle(em, p0, ej) - 2.0 * kPi;
+      c.kite_ring[b + j] = k;
+      ksum += k;
+      pm = p0; p0 = pn; em = ej;
+    }
+    area -= (d - 2) * kPi;
+    c.area_cell[i] = area;
+    double dev = fabs(ksum / area - 1.0);                           // sum of R over the cell, MM:469-475
+    atomicMax((unsigned long long*)(c.sums + 3), (unsigned long long)__double_as_longlong(dev));
+  }
+  m_block_add(area, c.sums);
+  m_block_add(ksum, c.sums + 2);
+}
+
+// per Voronoi vertex (= triangle slot): cellsOnVertex / edgesOnVertex in the reference's final
+// order (DV:504-582), areaTriangle (MM:310-322), kiteAreasOnVertex (MM:324-341)
+__global__ void fm_mpas_vertices(MpasCtx c) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  double area = 0.0;
+  if (t < c.n_tri) {
+    I4 v = c.row[t].v;
+    P4 q[3] = {c.pts[v.x], c.pts[v.y], c.pts[v.z]};
+    int ed[3], kmin = 0;
+    double kite[3];
+    for (int k = 0; k < 3; k++) {
+      int cell = (int)q[k].id, b = c.off[cell], d = c.off[cell + 1] - b, pos = -1;
+      for (int j = 0; j < d; j++)
+        if (c.ring_tri[b + j] == t + 1) { pos = b + j; break; }
+      if (pos < 0) { atomicOr(c.err, FM_E_TOPOLOGY); return; }
+      ed[k] = c.ring_edge[pos];   // edge (v[k], v[k-1]): the first of the two edges at v[k], counter-clockwise
+      kite[k] = c.kite_ring[pos];
+    }
+    for (int k = 1; k < 3; k++)
+      if (ed[k] < ed[kmin]) kmin = k;
+    for (int k = 0; k < 3; k++) {
+      int s = (kmin + k) % 3;
+      c.edges_on_vertex[3 * (size_t)t + k] = ed[s];
+      c.cells_on_vertex[3 * (size_t)t + k] = (int)q[s].id + 1;
+      c.kite_vtx[3 * (size_t)t + k] = kite[s];
+    }
+    P3 a = m_p3(q[0]), b = m_p3(q[1]), cc = m_p3(q[2]);
+    area = m_angle(cc, a, b) + m_angle(a, b, cc) + m_angle(b, cc, a) - kPi;
+    c.area_tri[t] = area;
+  }
+  m_block_add(area, c.sums + 1);
+}
+
+// per edge: edgesOnEdge (MM:271-294) and weightsOnEdge (calc_weightsOnEdge, MM:505-556).
+// For the i-th edge after e around cell c (counter-clockwise, n edges): the kite fractions
+// R = kite / areaCell of the vertices from that edge's end round to the START of e in c are
+// summed, then  w = n_sign / t_sign (sum - 1/2) dvEdge(edge) / dcEdge(e).
+__device__ __forceinline__ int m_ring_pos(const MpasCtx& c, int cell, int e1) {
+  int b = c.off[cell], d = c.off[cell + 1] - b;
+  for (int j = 0; j < d; j++)
+    if (c.ring_edge[b + j] == e1) return j;
+  return -1;
+}
+__global__ void fm_mpas_weights(MpasCtx c) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= c.n_edge) return;
+  const int stride = 2 * c.max_edges;
+  int* eoe = c.eoe + (size_t)stride * e;
+  double* w = c.weights + (size_t)stride * e;
+  int out = 0;
+  for (int side = 0; side < 2; side++) {
+    int cell = c.de[2 * e + side] - 1;
+    int b = c.off[cell], d = c.off[cell + 1] - b;
+    int l = m_ring_pos(c, cell, e + 1);
+    if (l < 0) { atomicOr(c.err, FM_E_TOPOLOGY); return; }
+    int vfinal = c.ring_tri[b + l];                                  // verticesOnCell(l): where e starts in this cell
+    double tsign = (vfinal == c.ve_vvt[2 * e]) ? 1.0 : -1.0;        // MM:491-503
+    double area = c.area_cell[cell];
+    for (int i = 1; i < d; i++) {
+      int le = l + i;                                                // iLocalEdge
+      if (le >= d) le -= d;
+      int e2 = c.ring_edge[b + le];
+      double s = 0.0;
+      int lv = le;
+      for (int j = 0; j < d - i; j++) {                              // jEnd = n - i vertices
+        lv = (lv + 1 == d) ? 0 : lv + 1;
+        s += c.kite_ring[b + lv] / area;
+      }
+      double nsign = (cell + 1 == c.de[2 * (size_t)(e2 - 1)]) ? 1.0 : -1.0;   // MM:477-489
+      double val = nsign / tsign * (s - 0.5);
+      val = val * c.dv[e2 - 1] / c.dc[e];
+      if (out < stride) { eoe[out] = e2; w[out] = val; }
+      out++;
+    }
+  }
+  c.n_eoe[e] = out;                                                  // = n1 + n2 - 2, MM:271
+  for (int k = out; k < stride; k++) { eoe[k] = 0; w[k] = 0.0; }
+}
+
+}  // namespace fm

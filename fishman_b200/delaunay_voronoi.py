@@ -152,6 +152,47 @@ class Mesh:
         self._chk(_lib.lib().fm_get_edges(self._h, _i(de), _i(vv), _i(vc)))
         return de, vv, vc
 
+    def mpas(self, strict=True):
+        """mpas_mesh_adapt + calc_weightsOnEdge (src/mpas_mesh_mod.F90:181-345, :442-561) on the
+        device, after voronoi_diagram(all=True).  Returns a dict of arrays named like the MPAS
+        variables (mpas_mesh_type, MM:25-73); ids 1-based, per-cell rows padded with 0 to
+        maxEdges = the largest degree found."""
+        L = _lib.lib()
+        me = C.c_int32(0)
+        self._chk(L.fm_mpas(self._h, 1 if strict else 0, C.byref(me)))
+        ME, n, nT, nE = me.value, self.n, self.n_tri, self.n_edge
+        i32, f64 = np.int32, np.float64
+        o = dict(maxEdges=ME, nCells=n, nEdges=nE, nVertices=nT,
+                 xyzEdge=np.empty((nE, 3), f64), lonlatEdge=np.empty((nE, 2), f64),
+                 dvEdge=np.empty(nE, f64), dcEdge=np.empty(nE, f64), dv1Edge=np.empty(nE, f64),
+                 dv2Edge=np.empty(nE, f64), angleEdge=np.empty(nE, f64), areaCell=np.empty(n, f64),
+                 cellsOnVertex=np.empty((nT, 3), i32), edgesOnVertex=np.empty((nT, 3), i32),
+                 areaTriangle=np.empty(nT, f64), kiteAreasOnVertex=np.empty((nT, 3), f64),
+                 nEdgesOnEdge=np.empty(nE, i32), edgesOnEdge=np.empty((nE, 2 * ME), i32),
+                 weightsOnEdge=np.empty((nE, 2 * ME), f64))
+        self._chk(L.fm_get_mpas_edges(self._h, _d(o["xyzEdge"]), _d(o["lonlatEdge"]), _d(o["dvEdge"]), _d(o["dcEdge"]),
+                                      _d(o["dv1Edge"]), _d(o["dv2Edge"]), _d(o["angleEdge"])))
+        ring_edge = np.empty(3 * nT, i32)
+        kite_ring = np.empty(3 * nT, f64)
+        self._chk(L.fm_get_mpas_cells(self._h, _i(ring_edge), _d(o["areaCell"]), _d(kite_ring)))
+        self._chk(L.fm_get_mpas_vertices(self._h, _i(o["cellsOnVertex"]), _i(o["edgesOnVertex"]),
+                                         _d(o["areaTriangle"]), _d(o["kiteAreasOnVertex"])))
+        self._chk(L.fm_get_mpas_edges_on_edge(self._h, _i(o["nEdgesOnEdge"]), _i(o["edgesOnEdge"]),
+                                              _d(o["weightsOnEdge"])))
+        de, vv, vc = self.edges()
+        o["cellsOnEdge"], o["verticesOnEdge"] = vc, vv
+        off, rt, rn = self.rings()
+        deg = np.diff(off)
+        o["nEdgesOnCell"] = deg.astype(i32)
+        cell = np.repeat(np.arange(n), deg)
+        pos = np.arange(len(rt)) - off[:-1][cell]
+        for name, src in (("verticesOnCell", rt), ("cellsOnCell", rn), ("edgesOnCell", ring_edge)):
+            a = np.zeros((n, ME), i32)
+            a[cell, pos] = src
+            o[name] = a
+        o["kiteAreasOnCell"] = (off, kite_ring)
+        return o
+
     def generators(self):
         g = np.empty((3, self.n))
         self._chk(_lib.lib().fm_get_generators(self._h, _d(g[0]), _d(g[1]), _d(g[2])))

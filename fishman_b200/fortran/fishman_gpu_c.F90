@@ -20,6 +20,7 @@ module fishman_gpu_c
   public :: fm_create, fm_create_lonlat, fm_create_dist, fm_destroy, fm_last_error
   public :: fm_triangulate, fm_retriangulate, fm_counts, fm_get_triangles
   public :: fm_voronoi, fm_get_circumcentres, fm_get_rings, fm_get_edges
+  public :: fm_mpas, fm_get_mpas_edges, fm_get_mpas_cells, fm_get_mpas_vertices, fm_get_mpas_edges_on_edge
   public :: fm_lloyd, fm_lloyd_local, fm_generator_block, fm_peer_handle, fm_peer_attach
   public :: fm_get_generators, fm_set_generators
   public :: fm_error_message
@@ -117,6 +118,43 @@ module fishman_gpu_c
     end function fm_get_edges
 
     ! Lloyd loop: no reference procedure (SURVEY.md F1)
+    ! mpas_mesh_adapt + calc_weightsOnEdge on the device (src/mpas_mesh_mod.F90:181-345, :442-561)
+    integer(c_int) function fm_mpas(h, strict, max_edges) bind(C, name='fm_mpas')
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), value :: strict
+      integer(c_int32_t), intent(out) :: max_edges
+    end function fm_mpas
+
+    integer(c_int) function fm_get_mpas_edges(h, xyz, lonlat, dv, dc, dv1, dv2, angle) bind(C, name='fm_get_mpas_edges')
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      real(c_double), intent(out) :: xyz(3,*), lonlat(2,*), dv(*), dc(*), dv1(*), dv2(*), angle(*)
+    end function fm_get_mpas_edges
+
+    integer(c_int) function fm_get_mpas_cells(h, edges_on_cell, area_cell, kite_on_cell) bind(C, name='fm_get_mpas_cells')
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: edges_on_cell(*)
+      real(c_double), intent(out) :: area_cell(*), kite_on_cell(*)
+    end function fm_get_mpas_cells
+
+    integer(c_int) function fm_get_mpas_vertices(h, cells_on_vertex, edges_on_vertex, area_triangle, kite) &
+        bind(C, name='fm_get_mpas_vertices')
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: cells_on_vertex(3,*), edges_on_vertex(3,*)
+      real(c_double), intent(out) :: area_triangle(*), kite(3,*)
+    end function fm_get_mpas_vertices
+
+    integer(c_int) function fm_get_mpas_edges_on_edge(h, n_edges_on_edge, edges_on_edge, weights_on_edge) &
+        bind(C, name='fm_get_mpas_edges_on_edge')
+      import :: c_int, c_int32_t, c_double, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: n_edges_on_edge(*), edges_on_edge(*)
+      real(c_double), intent(out) :: weights_on_edge(*)
+    end function fm_get_mpas_edges_on_edge
+
     integer(c_int) function fm_lloyd(h, rho, max_iter, tol, warm, iters, max_disp) bind(C, name='fm_lloyd')
       import :: c_int, c_int32_t, c_double, c_ptr, fm_density
       type(c_ptr), value :: h

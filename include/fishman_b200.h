@@ -83,6 +83,32 @@ int fm_get_rings(fm_handle* h, int32_t* off, int32_t* ring_tri, int32_t* ring_nb
  * Voronoi diagram is the dual of Delaunay edge k (DV:435-460). */
 int fm_get_edges(fm_handle* h, int32_t* de, int32_t* ve_vvt, int32_t* ve_vc);
 
+/* The arithmetic of the MPAS adapter, on the device: mpas_mesh_adapt (MM:181-345) and
+ * calc_weightsOnEdge (MM:442-561).  Needs fm_voronoi(h, 1).  *max_edges receives the largest cell
+ * degree (the reference hard-codes maxEdges = 6, MM:19).  strict != 0 keeps the reference's fatal
+ * checks (cell / triangle / kite areas each sum to 4 pi within 1e-10, MM:306, :320, :339; the kite
+ * fractions of every cell sum to 1, MM:469-475) -- they fire on any obtuse Delaunay triangle.
+ * Index conventions are those the reference reaches after its order fix-ups (DV:462-582):
+ * ring position j of a cell = verticesOnCell(j), cellsOnCell(j), edgesOnCell(j), edge j running from
+ * vertex j to vertex j+1; around a Voronoi vertex counter-clockwise, cellsOnVertex(k) on the left of
+ * edgesOnVertex(k), starting at the vertex's lowest edge id.  Edge ids are those of fm_get_edges. */
+int fm_mpas(fm_handle* h, int32_t strict, int32_t* max_edges);
+/* per edge (E): xyz 3 x E (xEdge,yEdge,zEdge: intersect, SG:316-363), lonlat 2 x E, dvEdge, dcEdge,
+ * dv1Edge, dv2Edge, angleEdge (MM:244-266); any pointer may be NULL */
+int fm_get_mpas_edges(fm_handle* h, double* xyz, double* lonlat, double* dv, double* dc, double* dv1,
+                      double* dv2, double* angle);
+/* per cell, in the CSR layout of fm_get_rings (6N-12 entries): edgesOnCell and the kite area of
+ * (cell, ring vertex j) -- kiteAreasOnVertex seen from the cell; areaCell has N entries (MM:296-308) */
+int fm_get_mpas_cells(fm_handle* h, int32_t* edges_on_cell, double* area_cell, double* kite_on_cell);
+/* per Voronoi vertex (T): cellsOnVertex, edgesOnVertex, kiteAreasOnVertex 3 x T; areaTriangle T
+ * (MM:228-242, :310-341) */
+int fm_get_mpas_vertices(fm_handle* h, int32_t* cells_on_vertex, int32_t* edges_on_vertex,
+                         double* area_triangle, double* kite_areas_on_vertex);
+/* per edge: nEdgesOnEdge (E), edgesOnEdge and weightsOnEdge, rows of 2 * max_edges (MM:271-294,
+ * calc_weightsOnEdge MM:505-556; weights start from zero, which the reference forgets, MM:386/546) */
+int fm_get_mpas_edges_on_edge(fm_handle* h, int32_t* n_edges_on_edge, int32_t* edges_on_edge,
+                              double* weights_on_edge);
+
 /* Lloyd loop (no reference code).  Runs at most max_iter iterations of
  * triangulate -> circumcentres -> centroids -> generator update, stopping early when the
  * largest chord displacement is <= tol.  warm != 0 repairs the previous triangulation by

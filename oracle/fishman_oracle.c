@@ -30,6 +30,11 @@
  *      never compared.
  *  D4  the Lloyd step does not exist in the reference; it is the
  *      specification of SURVEY 7.3, restated in fo_lloyd_step below.
+ *  D5  the MPAS adapter (fo_mpas, "MM:n" = src/mpas_mesh_mod.F90:n) sizes its
+ *      per-cell rows by the largest degree found instead of the reference's
+ *      fixed maxEdges = 6 (MM:19), zero-initialises weightsOnEdge
+ *      (the reference accumulates into an unset allocate, MM:386/546), and
+ *      fills the padded slots of the per-cell index rows with 0.
  *
  * Build: gcc -O2 -ffp-contract=off -shared -fPIC (see oracle/Makefile).
  */
@@ -90,8 +95,10 @@ typedef struct fo_mesh {
   double *cx, *cy, *cz, *clon, *clat;
   int *ring_off, *ring_tri, *ring_nbr;
   int have_dt, have_vd;
+  struct fo_mpas *mp; /* MPAS adapter arrays (fo_mpas) */
   char err[512];
 } fo_mesh;
+static void mpas_free(fo_mesh *m);
 
 /* ------------------------------------------------------------------ geometry */
 
@@ -636,6 +643,7 @@ void fo_destroy(fo_mesh *m) {
   free(m->obs); free(m->tmp); free(m->tri); free(m->adj);
   free(m->cx); free(m->cy); free(m->cz); free(m->clon); free(m->clat);
   free(m->ring_off); free(m->ring_tri); free(m->ring_nbr);
+  mpas_free(m);
   free(m);
 }
 
@@ -1061,5 +1069,375 @@ int fo_areas(fo_mesh *m, double *area_cell, double *area_tri, double *sum_cell, 
     stt += a;
   }
   *sum_cell = sc; *sum_tri = stt;
+  return 0;
+}
+
+/* ------------------------------------------- MPAS adapter arithmetic (MM) */
+/* Restates mpas_mesh_adapt (MM:181-345) and calc_weightsOnEdge (MM:442-561) on
+   flat arrays, with the container graph the reference walks rebuilt first:
+   Delaunay / Voronoi edges in creation order (DV:413-460) and the ordered
+   VE-in-VC, VE-in-VVT, VC-in-VVT lists (DV:462-582).  0-based inside, 1-based
+   through the getters; rows of per-cell arrays have stride maxEdges, rows of
+   edgesOnEdge / weightsOnEdge stride maxEdges2 = 2 maxEdges (deviation D5). */
+typedef struct fo_mpas {
+  int nCells, nEdges, nVertices, maxEdges, maxEdges2;
+  int *cellsOnEdge, *verticesOnEdge, *nEdgesOnEdge, *edgesOnEdge;
+  double *xEdge, *yEdge, *zEdge, *lonEdge, *latEdge;
+  double *dvEdge, *dcEdge, *dv1Edge, *dv2Edge, *angleEdge, *weightsOnEdge;
+  int *nEdgesOnCell, *verticesOnCell, *cellsOnCell, *edgesOnCell;
+  double *areaCell;
+  int *cellsOnVertex, *edgesOnVertex;
+  double *areaTriangle, *kiteAreasOnVertex;
+} fo_mpas_t;
+
+static void mpas_free(fo_mesh *m) {
+  fo_mpas_t *p = m->mp;
+  if (!p) return;
+  free(p->cellsOnEdge); free(p->verticesOnEdge); free(p->nEdgesOnEdge); free(p->edgesOnEdge);
+  free(p->xEdge); free(p->yEdge); free(p->zEdge); free(p->lonEdge); free(p->latEdge);
+  free(p->dvEdge); free(p->dcEdge); free(p->dv1Edge); free(p->dv2Edge); free(p->angleEdge);
+  free(p->weightsOnEdge);
+  free(p->nEdgesOnCell); free(p->verticesOnCell); free(p->cellsOnCell); free(p->edgesOnCell);
+  free(p->areaCell); free(p->cellsOnVertex); free(p->edgesOnVertex);
+  free(p->areaTriangle); free(p->kiteAreasOnVertex);
+  free(p);
+  m->mp = NULL;
+}
+
+static double dot3(const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+/* SG:289-296 calc_arc_length */
+static double calc_arc_length(const double *a, const double *b) {
+  return acos(fmax(fmin(dot3(a, b), 1.0), -1.0));
+}
+
+/* SG:316-363 intersect: great circles (a,b) and (c,d); e = the intersection between
+   the end points, through lon/lat and back as the reference does.  0 = none. */
+static int sg_intersect(const double *a, const double *b, const double *c, const double *d,
+                        double *e, double *elon, double *elat) {
+  double n1[3], n2[3], v[3], r, lon1, lon2, lat1, lat2, ae[3], be[3], ce[3], de[3];
+  cross3(a, b, n1);
+  cross3(c, d, n2);
+  cross3(n1, n2, v);
+  r = sqrt(dot3(v, v));
+  if (r > FO_EPS) { v[0] /= r; v[1] /= r; v[2] /= r; } else return 0;
+  lat1 = asin(v[2]);
+  lat2 = -lat1;
+  lon1 = atan2(v[1], v[0]);
+  lon2 = lon1 - FO_PI;
+  if (lon1 < 0.0) lon1 += FO_PI2;
+  if (lon1 > FO_PI2) lon1 -= FO_PI2;
+  if (lon2 < 0.0) lon2 += FO_PI2;
+  if (lon2 > FO_PI2) lon2 -= FO_PI2;
+  *elon = lon1; *elat = lat1;
+  cartesian_transform(lon1, lat1, &e[0], &e[1], &e[2]);
+  cross3(a, e, ae); cross3(b, e, be); cross3(c, e, ce); cross3(d, e, de);
+  if (dot3(ae, be) >= 0 || dot3(ce, de) >= 0) {
+    *elon = lon2; *elat = lat2;
+    cartesian_transform(lon2, lat2, &e[0], &e[1], &e[2]);
+  }
+  return 1;
+}
+
+#define MP_ALLOC(field, type, count) p->field = (type *)calloc((size_t)(count) > 0 ? (size_t)(count) : 1, sizeof(type))
+
+/* strict != 0: the reference's run-time checks are fatal (MM:306, :320, :339, :469-475) -- they fire
+   on any mesh with an obtuse Delaunay triangle; strict == 0: the arithmetic is carried through. */
+int fo_mpas(fo_mesh *m, int strict, int *max_edges_out) {
+  int n = m->n, nT = m->nT, nE, i, j, k, e, t, maxEdges = 0, ME, ME2;
+  fo_mpas_t *p;
+  int *ring_edge; /* per ring position: the edge to ring_nbr (VE-in-VC, ordered: DV:462-503) */
+  if (!m->have_vd) return fo_fail(m, "mpas_mesh_output before voronoi_diagram");
+  mpas_free(m);
+  p = m->mp = (fo_mpas_t *)calloc(1, sizeof(fo_mpas_t));
+  nE = nT + n - 2; /* euler_formula, SG:57-71 */
+  for (i = 0; i < n; i++) {
+    int d = m->ring_off[i + 1] - m->ring_off[i];
+    if (d > maxEdges) maxEdges = d;
+  }
+  ME = p->maxEdges = maxEdges; ME2 = p->maxEdges2 = 2 * maxEdges;
+  p->nCells = n; p->nEdges = nE; p->nVertices = nT;
+  if (max_edges_out) *max_edges_out = ME;
+  MP_ALLOC(cellsOnEdge, int, 2 * nE); MP_ALLOC(verticesOnEdge, int, 2 * nE);
+  MP_ALLOC(nEdgesOnEdge, int, nE); MP_ALLOC(edgesOnEdge, int, (size_t)ME2 * nE);
+  MP_ALLOC(xEdge, double, nE); MP_ALLOC(yEdge, double, nE); MP_ALLOC(zEdge, double, nE);
+  MP_ALLOC(lonEdge, double, nE); MP_ALLOC(latEdge, double, nE);
+  MP_ALLOC(dvEdge, double, nE); MP_ALLOC(dcEdge, double, nE); MP_ALLOC(dv1Edge, double, nE);
+  MP_ALLOC(dv2Edge, double, nE); MP_ALLOC(angleEdge, double, nE);
+  MP_ALLOC(weightsOnEdge, double, (size_t)ME2 * nE);
+  MP_ALLOC(nEdgesOnCell, int, n); MP_ALLOC(verticesOnCell, int, (size_t)ME * n);
+  MP_ALLOC(cellsOnCell, int, (size_t)ME * n); MP_ALLOC(edgesOnCell, int, (size_t)ME * n);
+  MP_ALLOC(areaCell, double, n);
+  MP_ALLOC(cellsOnVertex, int, 3 * nT); MP_ALLOC(edgesOnVertex, int, 3 * nT);
+  MP_ALLOC(areaTriangle, double, nT); MP_ALLOC(kiteAreasOnVertex, double, 3 * nT);
+  for (i = 0; i < (int)((size_t)ME * n); i++) p->verticesOnCell[i] = p->cellsOnCell[i] = p->edgesOnCell[i] = -1;
+  for (i = 0; i < ME2 * nE; i++) p->edgesOnEdge[i] = -1;
+
+  /* Delaunay + Voronoi edges, DV:413-460: cell i creates the edge to every ring
+     neighbour with a larger id, in ring order; VVT1 = ring(j), VVT2 = ring(j+1) */
+  ring_edge = (int *)malloc(sizeof(int) * (3 * (size_t)nT + 1));
+  e = 0;
+  for (i = 0; i < n; i++) {
+    int o = m->ring_off[i], d = m->ring_off[i + 1] - o;
+    for (j = 0; j < d; j++) {
+      int nb = m->ring_nbr[o + j];
+      if (nb > i) {
+        if (e >= nE) { free(ring_edge); return fo_fail(m, "more edges than euler_formula allows"); }
+        p->cellsOnEdge[2 * e] = i; p->cellsOnEdge[2 * e + 1] = nb;
+        p->verticesOnEdge[2 * e] = m->ring_tri[o + j];
+        p->verticesOnEdge[2 * e + 1] = m->ring_tri[o + (j + 1) % d];
+        ring_edge[o + j] = e;
+        e++;
+      }
+    }
+  }
+  if (e != nE) { free(ring_edge); return fo_fail(m, "edge count differs from euler_formula"); }
+  /* the other cell of each edge finds it at the ring position of the creator */
+  for (i = 0; i < n; i++) {
+    int o = m->ring_off[i], d = m->ring_off[i + 1] - o;
+    for (j = 0; j < d; j++) {
+      int nb = m->ring_nbr[o + j];
+      if (nb < i) {
+        int o2 = m->ring_off[nb], d2 = m->ring_off[nb + 1] - o2, q;
+        for (q = 0; q < d2; q++) if (m->ring_nbr[o2 + q] == i) break;
+        if (q == d2) { free(ring_edge); return fo_fail(m, "Internal error! (edge not found in the neighbour's ring)"); }
+        ring_edge[o + j] = ring_edge[o2 + q];
+      }
+    }
+  }
+  /* cells, MM:205-226.  VE-in-VC after the fix-up of DV:462-503: edge k runs from
+     vertex k to vertex k+1 with the cell on its left, i.e. it is the edge to adjVC(k) */
+  for (i = 0; i < n; i++) {
+    int o = m->ring_off[i], d = m->ring_off[i + 1] - o;
+    p->nEdgesOnCell[i] = d;
+    for (j = 0; j < d; j++) {
+      p->verticesOnCell[(size_t)ME * i + j] = m->ring_tri[o + j];
+      p->cellsOnCell[(size_t)ME * i + j] = m->ring_nbr[o + j];
+      p->edgesOnCell[(size_t)ME * i + j] = ring_edge[o + j];
+    }
+  }
+  /* vertices, MM:228-242.  VE-in-VVT / VC-in-VVT after the fix-ups of DV:504-582:
+     counter-clockwise, VC(i) on the left of VE(i) seen from the vertex, starting at
+     the first edge appended to the vertex = its lowest edge id (DV:454-455) */
+  for (t = 0; t < nT; t++) {
+    int ed[3], kmin = 0;
+    for (k = 0; k < 3; k++) {
+      int v = m->tri[3 * t + k], o = m->ring_off[v], d = m->ring_off[v + 1] - o, q;
+      for (q = 0; q < d; q++) if (m->ring_tri[o + q] == t) break;
+      if (q == d) { free(ring_edge); return fo_fail(m, "Internal error! (vertex not in the ring of its cell)"); }
+      ed[k] = ring_edge[o + q]; /* edge (v[k], v[k-1]): ring_nbr = the vertex before v in t */
+      if (m->ring_nbr[o + q] != m->tri[3 * t + IM1[k]]) { free(ring_edge); return fo_fail(m, "Internal error! (ring pairing)"); }
+    }
+    for (k = 1; k < 3; k++) if (ed[k] < ed[kmin]) kmin = k;
+    for (k = 0; k < 3; k++) {
+      p->edgesOnVertex[3 * t + k] = ed[(kmin + k) % 3];
+      p->cellsOnVertex[3 * t + k] = m->tri[3 * t + (kmin + k) % 3];
+    }
+    /* order consistency check, DV:570-581 */
+    for (k = 0; k < 3; k++) {
+      int ee = p->edgesOnVertex[3 * t + k], cc = p->cellsOnVertex[3 * t + k];
+      if (p->verticesOnEdge[2 * ee] == t) { if (p->cellsOnEdge[2 * ee] != cc) { free(ring_edge); return fo_fail(m, "Internal error! (DV:576)"); } }
+      else if (p->cellsOnEdge[2 * ee + 1] != cc) { free(ring_edge); return fo_fail(m, "Internal error! (DV:578)"); }
+    }
+  }
+  free(ring_edge);
+
+  /* edges, MM:244-294 */
+  for (e = 0; e < nE; e++) {
+    int c1 = p->cellsOnEdge[2 * e], c2 = p->cellsOnEdge[2 * e + 1];
+    int v1 = p->verticesOnEdge[2 * e], v2 = p->verticesOnEdge[2 * e + 1];
+    double A[3], B[3], Cc[3], D[3], X[3], xp[3], lon, lat, xlon;
+    int i1 = -1, i2 = -1, d1 = p->nEdgesOnCell[c1], d2 = p->nEdgesOnCell[c2];
+    A[0] = m->x[c1]; A[1] = m->y[c1]; A[2] = m->z[c1];
+    B[0] = m->x[c2]; B[1] = m->y[c2]; B[2] = m->z[c2];
+    Cc[0] = m->cx[v1]; Cc[1] = m->cy[v1]; Cc[2] = m->cz[v1];
+    D[0] = m->cx[v2]; D[1] = m->cy[v2]; D[2] = m->cz[v2];
+    if (!sg_intersect(A, B, Cc, D, X, &lon, &lat)) return fo_fail(m, "Unable to find intersection between DE and VE!");
+    p->lonEdge[e] = lon; p->latEdge[e] = lat;
+    p->xEdge[e] = X[0]; p->yEdge[e] = X[1]; p->zEdge[e] = X[2];
+    p->dvEdge[e] = calc_arc_length(Cc, D);
+    p->dcEdge[e] = calc_arc_length(A, B);
+    p->dv1Edge[e] = calc_arc_length(Cc, X);
+    p->dv2Edge[e] = calc_arc_length(D, X);
+    xlon = m->lon[c1] + 0.1 * FO_PI;          /* MM:262-266 */
+    if (xlon > FO_PI2) xlon -= FO_PI2;
+    cartesian_transform(xlon, m->lat[c1], &xp[0], &xp[1], &xp[2]);
+    p->angleEdge[e] = calc_sphere_angle(xp, A, B);
+    p->nEdgesOnEdge[e] = d1 + d2 - 2;         /* MM:271 */
+    j = 0;
+    for (k = 0; k < d1; k++) if (p->edgesOnCell[(size_t)ME * c1 + k] == e) i1 = k; /* index_ptr, MM:274 */
+    for (k = 0; k < d2; k++) if (p->edgesOnCell[(size_t)ME * c2 + k] == e) i2 = k;
+    if (i1 < 0 || i2 < 0) return fo_fail(m, "Internal error! (edge not on its cells)");
+    for (k = i1 + 1; k < d1; k++) p->edgesOnEdge[(size_t)ME2 * e + j++] = p->edgesOnCell[(size_t)ME * c1 + k];
+    for (k = 0; k < i1; k++) p->edgesOnEdge[(size_t)ME2 * e + j++] = p->edgesOnCell[(size_t)ME * c1 + k];
+    for (k = i2 + 1; k < d2; k++) p->edgesOnEdge[(size_t)ME2 * e + j++] = p->edgesOnCell[(size_t)ME * c2 + k];
+    for (k = 0; k < i2; k++) p->edgesOnEdge[(size_t)ME2 * e + j++] = p->edgesOnCell[(size_t)ME * c2 + k];
+  }
+
+  /* areas, MM:296-341 (each total within 1e-10 of 4 pi) */
+  {
+    double total = 0.0, px[64], py[64], pz[64];
+    if (ME > 64) return fo_fail(m, "cell degree > 64");
+    for (i = 0; i < n; i++) {
+      int d = p->nEdgesOnCell[i];
+      for (k = 0; k < d; k++) {
+        int vv = p->verticesOnCell[(size_t)ME * i + k];
+        px[k] = m->cx[vv]; py[k] = m->cy[vv]; pz[k] = m->cz[vv];
+      }
+      p->areaCell[i] = fo_calc_area(d, px, py, pz);
+      total += p->areaCell[i];
+    }
+    if (strict && fabs(total - 4 * FO_PI) > 1.0e-10) return fo_fail(m, "Too large total cell area error!");
+    total = 0.0;
+    for (t = 0; t < nT; t++) {
+      for (k = 0; k < 3; k++) {
+        int v = m->tri[3 * t + k];
+        px[k] = m->x[v]; py[k] = m->y[v]; pz[k] = m->z[v];
+      }
+      p->areaTriangle[t] = fo_calc_area(3, px, py, pz);
+      total += p->areaTriangle[t];
+    }
+    if (strict && fabs(total - 4 * FO_PI) > 1.0e-10) return fo_fail(m, "Too large total triangle area error!");
+    total = 0.0;
+    for (t = 0; t < nT; t++) {
+      for (k = 0; k < 3; k++) {
+        const int e1 = p->edgesOnVertex[3 * t + k], e2 = p->edgesOnVertex[3 * t + (k + 1) % 3];
+        int vc = p->cellsOnVertex[3 * t + k];
+        px[0] = p->xEdge[e1]; py[0] = p->yEdge[e1]; pz[0] = p->zEdge[e1];
+        px[1] = m->x[vc]; py[1] = m->y[vc]; pz[1] = m->z[vc];
+        px[2] = p->xEdge[e2]; py[2] = p->yEdge[e2]; pz[2] = p->zEdge[e2];
+        px[3] = m->cx[t]; py[3] = m->cy[t]; pz[3] = m->cz[t];
+        p->kiteAreasOnVertex[3 * t + k] = fo_calc_area(4, px, py, pz);
+        total += p->kiteAreasOnVertex[3 * t + k];
+      }
+    }
+    if (strict && fabs(total - 4 * FO_PI) > 1.0e-10) return fo_fail(m, "Too large total kite area error!");
+  }
+
+  /* calc_weightsOnEdge, MM:442-561 (weights start at zero: deviation D5) */
+  {
+    double *R = (double *)calloc((size_t)ME * n, sizeof(double));
+    int *nrm = (int *)calloc((size_t)ME * n, sizeof(int)), *tng = (int *)calloc(3 * (size_t)nT, sizeof(int));
+    int iVertex, iLocalCell, iLocalVertex, iLocalEdge, iCell, iEdge, bad = 0;
+    for (iVertex = 0; iVertex < nT && !bad; iVertex++)          /* MM:458-468 */
+      for (iLocalCell = 0; iLocalCell < 3; iLocalCell++) {
+        iCell = p->cellsOnVertex[3 * iVertex + iLocalCell];
+        for (iLocalVertex = 0; iLocalVertex < p->nEdgesOnCell[iCell]; iLocalVertex++)
+          if (p->verticesOnCell[(size_t)ME * iCell + iLocalVertex] == iVertex) break;
+        if (iLocalVertex >= p->nEdgesOnCell[iCell]) { bad = 1; break; }
+        R[(size_t)ME * iCell + iLocalVertex] = p->kiteAreasOnVertex[3 * iVertex + iLocalCell] / p->areaCell[iCell];
+      }
+    for (iCell = 0; iCell < n && !bad; iCell++) {               /* MM:469-475 */
+      double s = 0.0;
+      for (k = 0; k < p->nEdgesOnCell[iCell]; k++) s += R[(size_t)ME * iCell + k];
+      if (strict && fabs(s - 1.0) > 1.0e-10) bad = 2;
+    }
+    for (iCell = 0; iCell < n && !bad; iCell++)                 /* MM:477-489 */
+      for (iLocalEdge = 0; iLocalEdge < p->nEdgesOnCell[iCell]; iLocalEdge++) {
+        iEdge = p->edgesOnCell[(size_t)ME * iCell + iLocalEdge];
+        if (iCell == p->cellsOnEdge[2 * iEdge]) nrm[(size_t)ME * iCell + iLocalEdge] = 1;
+        else if (iCell == p->cellsOnEdge[2 * iEdge + 1]) nrm[(size_t)ME * iCell + iLocalEdge] = -1;
+        else bad = 3;
+      }
+    for (iVertex = 0; iVertex < nT && !bad; iVertex++)          /* MM:491-503 */
+      for (iLocalEdge = 0; iLocalEdge < 3; iLocalEdge++) {
+        iEdge = p->edgesOnVertex[3 * iVertex + iLocalEdge];
+        if (iVertex == p->verticesOnEdge[2 * iEdge]) tng[3 * iVertex + iLocalEdge] = 1;
+        else if (iVertex == p->verticesOnEdge[2 * iEdge + 1]) tng[3 * iVertex + iLocalEdge] = -1;
+        else bad = 4;
+      }
+    for (iEdge = 0; iEdge < nE && !bad; iEdge++) {              /* MM:505-556 */
+      int iCell1 = p->cellsOnEdge[2 * iEdge], iCell2 = p->cellsOnEdge[2 * iEdge + 1];
+      int n1 = p->nEdgesOnCell[iCell1], n2 = p->nEdgesOnCell[iCell2];
+      int iLocalEdge1 = -1, iLocalEdge2 = -1, ii;
+      for (k = 0; k < n1; k++) if (p->edgesOnCell[(size_t)ME * iCell1 + k] == iEdge) { iLocalEdge1 = k + 1; break; }
+      for (k = 0; k < n2; k++) if (p->edgesOnCell[(size_t)ME * iCell2 + k] == iEdge) { iLocalEdge2 = k + 1; break; }
+      if (iLocalEdge1 < 0 || iLocalEdge2 < 0) { bad = 5; break; }
+      for (ii = 1; ii <= p->nEdgesOnEdge[iEdge]; ii++) {          /* 1-based local indices, as MM */
+        int iEdgeOnEdge = p->edgesOnEdge[(size_t)ME2 * iEdge + ii - 1];
+        int nEdgesOnCell, jEnd, iLocalEdgeOnVertex;
+        double w = 0.0;
+        iVertex = -1;
+        if (p->cellsOnEdge[2 * iEdgeOnEdge] == iCell1 || p->cellsOnEdge[2 * iEdgeOnEdge + 1] == iCell1) {
+          iCell = iCell1; nEdgesOnCell = n1; jEnd = n1 - ii; iLocalEdge = iLocalEdge1 + ii;
+        } else if (p->cellsOnEdge[2 * iEdgeOnEdge] == iCell2 || p->cellsOnEdge[2 * iEdgeOnEdge + 1] == iCell2) {
+          iCell = iCell2; nEdgesOnCell = n2; jEnd = n2 - ii + n1 - 1; iLocalEdge = iLocalEdge2 + ii - n1 + 1;
+        } else { bad = 6; break; }
+        if (iLocalEdge > nEdgesOnCell) iLocalEdge -= nEdgesOnCell;
+        iLocalVertex = iLocalEdge;
+        for (j = 1; j <= jEnd; j++) {
+          iLocalVertex++;
+          if (iLocalVertex > nEdgesOnCell) iLocalVertex = 1;
+          iVertex = p->verticesOnCell[(size_t)ME * iCell + iLocalVertex - 1];
+          w += R[(size_t)ME * iCell + iLocalVertex - 1];
+        }
+        if (iVertex < 0) { bad = 7; break; }
+        for (iLocalEdgeOnVertex = 0; iLocalEdgeOnVertex < 3; iLocalEdgeOnVertex++)
+          if (p->edgesOnVertex[3 * iVertex + iLocalEdgeOnVertex] == iEdge) break;
+        if (iLocalEdgeOnVertex >= 3) { bad = 8; break; }
+        w = (double)nrm[(size_t)ME * iCell + iLocalEdge - 1] / (double)tng[3 * iVertex + iLocalEdgeOnVertex] * (w - 0.5);
+        w = w * p->dvEdge[iEdgeOnEdge] / p->dcEdge[iEdge];
+        p->weightsOnEdge[(size_t)ME2 * iEdge + ii - 1] = w;
+      }
+    }
+    free(R); free(nrm); free(tng);
+    if (bad) { snprintf(m->err, sizeof m->err, "Internal error! (calc_weightsOnEdge check %d)", bad); return 1; }
+  }
+  return 0;
+}
+
+/* getters: ids 1-based (unused slots 0); any pointer may be NULL */
+static void out_ids(int *dst, const int *src, size_t cnt) {
+  size_t i;
+  if (dst) for (i = 0; i < cnt; i++) dst[i] = src[i] + 1;
+}
+static void out_dbl(double *dst, const double *src, size_t cnt) {
+  if (dst) memcpy(dst, src, sizeof(double) * cnt);
+}
+int fo_mpas_get_edges(fo_mesh *m, int *cellsOnEdge, int *verticesOnEdge, double *xyz, double *lonlat,
+                      double *dv, double *dc, double *dv1, double *dv2, double *angle) {
+  fo_mpas_t *p = m->mp;
+  int e;
+  if (!p) return fo_fail(m, "fo_mpas_get_edges before fo_mpas");
+  out_ids(cellsOnEdge, p->cellsOnEdge, 2 * (size_t)p->nEdges);
+  out_ids(verticesOnEdge, p->verticesOnEdge, 2 * (size_t)p->nEdges);
+  for (e = 0; e < p->nEdges; e++) {
+    if (xyz) { xyz[3 * e] = p->xEdge[e]; xyz[3 * e + 1] = p->yEdge[e]; xyz[3 * e + 2] = p->zEdge[e]; }
+    if (lonlat) { lonlat[2 * e] = p->lonEdge[e]; lonlat[2 * e + 1] = p->latEdge[e]; }
+  }
+  out_dbl(dv, p->dvEdge, p->nEdges); out_dbl(dc, p->dcEdge, p->nEdges);
+  out_dbl(dv1, p->dv1Edge, p->nEdges); out_dbl(dv2, p->dv2Edge, p->nEdges);
+  out_dbl(angle, p->angleEdge, p->nEdges);
+  return 0;
+}
+int fo_mpas_get_cells(fo_mesh *m, int *nEdgesOnCell, int *verticesOnCell, int *cellsOnCell, int *edgesOnCell,
+                      double *areaCell) {
+  fo_mpas_t *p = m->mp;
+  size_t cnt;
+  if (!p) return fo_fail(m, "fo_mpas_get_cells before fo_mpas");
+  cnt = (size_t)p->maxEdges * p->nCells;
+  if (nEdgesOnCell) memcpy(nEdgesOnCell, p->nEdgesOnCell, sizeof(int) * p->nCells);
+  out_ids(verticesOnCell, p->verticesOnCell, cnt);
+  out_ids(cellsOnCell, p->cellsOnCell, cnt);
+  out_ids(edgesOnCell, p->edgesOnCell, cnt);
+  out_dbl(areaCell, p->areaCell, p->nCells);
+  return 0;
+}
+int fo_mpas_get_vertices(fo_mesh *m, int *cellsOnVertex, int *edgesOnVertex, double *areaTriangle, double *kite) {
+  fo_mpas_t *p = m->mp;
+  if (!p) return fo_fail(m, "fo_mpas_get_vertices before fo_mpas");
+  out_ids(cellsOnVertex, p->cellsOnVertex, 3 * (size_t)p->nVertices);
+  out_ids(edgesOnVertex, p->edgesOnVertex, 3 * (size_t)p->nVertices);
+  out_dbl(areaTriangle, p->areaTriangle, p->nVertices);
+  out_dbl(kite, p->kiteAreasOnVertex, 3 * (size_t)p->nVertices);
+  return 0;
+}
+int fo_mpas_get_edges_on_edge(fo_mesh *m, int *nEdgesOnEdge, int *edgesOnEdge, double *weightsOnEdge) {
+  fo_mpas_t *p = m->mp;
+  size_t cnt;
+  if (!p) return fo_fail(m, "fo_mpas_get_edges_on_edge before fo_mpas");
+  cnt = (size_t)p->maxEdges2 * p->nEdges;
+  if (nEdgesOnEdge) memcpy(nEdgesOnEdge, p->nEdgesOnEdge, sizeof(int) * p->nEdges);
+  out_ids(edgesOnEdge, p->edgesOnEdge, cnt);
+  out_dbl(weightsOnEdge, p->weightsOnEdge, cnt);
   return 0;
 }

@@ -77,6 +77,11 @@ def lib():
         L.fo_calc_area.restype = C.c_double
         L.fo_calc_area.argtypes = [C.c_int, dp, dp, dp]
         L.fo_areas.argtypes = [vp, dp, dp, dp, dp]
+        L.fo_mpas.argtypes = [vp, C.c_int, ip]
+        L.fo_mpas_get_edges.argtypes = [vp, ip, ip, dp, dp, dp, dp, dp, dp, dp]
+        L.fo_mpas_get_cells.argtypes = [vp, ip, ip, ip, ip, dp]
+        L.fo_mpas_get_vertices.argtypes = [vp, ip, ip, dp, dp]
+        L.fo_mpas_get_edges_on_edge.argtypes = [vp, ip, ip, dp]
         _lib = L
     return _lib
 
@@ -170,6 +175,40 @@ class Oracle:
         sc, st = C.c_double(), C.c_double()
         self._chk(lib().fo_areas(self._h, _d(ac), _d(at), C.byref(sc), C.byref(st)))
         return ac, at, sc.value, st.value
+
+
+    def mpas(self, strict=True):
+        """mpas_mesh_adapt + calc_weightsOnEdge (src/mpas_mesh_mod.F90:181-345, :442-561) as a dict
+        of arrays named like the MPAS variables; ids 1-based, rows padded with 0.  strict: the
+        reference's Sum = 4 pi +- 1e-10 checks are fatal (they fire on any obtuse Delaunay triangle)."""
+        me = C.c_int(0)
+        self._chk(lib().fo_mpas(self._h, 1 if strict else 0, C.byref(me)))
+        ME, n = me.value, self.n
+        nT = lib().fo_num_triangles(self._h)
+        nE = nT + n - 2
+        i32, f64 = np.int32, np.float64
+        o = dict(maxEdges=ME, nCells=n, nEdges=nE, nVertices=nT,
+                 cellsOnEdge=np.empty((nE, 2), i32), verticesOnEdge=np.empty((nE, 2), i32),
+                 xyzEdge=np.empty((nE, 3), f64), lonlatEdge=np.empty((nE, 2), f64),
+                 dvEdge=np.empty(nE, f64), dcEdge=np.empty(nE, f64), dv1Edge=np.empty(nE, f64),
+                 dv2Edge=np.empty(nE, f64), angleEdge=np.empty(nE, f64),
+                 nEdgesOnCell=np.empty(n, i32), verticesOnCell=np.empty((n, ME), i32),
+                 cellsOnCell=np.empty((n, ME), i32), edgesOnCell=np.empty((n, ME), i32), areaCell=np.empty(n, f64),
+                 cellsOnVertex=np.empty((nT, 3), i32), edgesOnVertex=np.empty((nT, 3), i32),
+                 areaTriangle=np.empty(nT, f64), kiteAreasOnVertex=np.empty((nT, 3), f64),
+                 nEdgesOnEdge=np.empty(nE, i32), edgesOnEdge=np.empty((nE, 2 * ME), i32),
+                 weightsOnEdge=np.empty((nE, 2 * ME), f64))
+        L = lib()
+        self._chk(L.fo_mpas_get_edges(self._h, _i(o["cellsOnEdge"]), _i(o["verticesOnEdge"]), _d(o["xyzEdge"]),
+                                      _d(o["lonlatEdge"]), _d(o["dvEdge"]), _d(o["dcEdge"]), _d(o["dv1Edge"]),
+                                      _d(o["dv2Edge"]), _d(o["angleEdge"])))
+        self._chk(L.fo_mpas_get_cells(self._h, _i(o["nEdgesOnCell"]), _i(o["verticesOnCell"]), _i(o["cellsOnCell"]),
+                                      _i(o["edgesOnCell"]), _d(o["areaCell"])))
+        self._chk(L.fo_mpas_get_vertices(self._h, _i(o["cellsOnVertex"]), _i(o["edgesOnVertex"]),
+                                         _d(o["areaTriangle"]), _d(o["kiteAreasOnVertex"])))
+        self._chk(L.fo_mpas_get_edges_on_edge(self._h, _i(o["nEdgesOnEdge"]), _i(o["edgesOnEdge"]),
+                                              _d(o["weightsOnEdge"])))
+        return o
 
 
 def canonical_triangles(tri):
