@@ -62,6 +62,8 @@ enum {
   FM_C_SLOWDONE = 9,   // blocks of the deferred kernel that have finished (self-reset)
   FM_C_MAXDISP = 10,   // 64-bit word: bits of the largest chord displacement ([10], [11])
   FM_C_ERR = 12,       // error bits (DtCtx::err points here in the CUDA library)
+  FM_C_REQ = 13,       // sharded sweep: flip requests this rank found
+  FM_C_BND = 14,       // sharded sweep: swept triangles with a vertex owned by another rank
   FM_C_STAMP = 15      // next unused stamp
 };
 
@@ -113,6 +115,16 @@ struct DtCtx {
   int* slow;                   // items whose fp64 filter was inconclusive (length in counters[8]);
                                // a second launch runs the exact predicates on them
   int* err;
+  // sharded warm sweep (fm_peer_attach; all zero otherwise): this rank sweeps the triangle slots
+  // [t_begin, t_begin + launch size).  A violated edge becomes a request (t << 2 | edge) in
+  // req[], a swept triangle with a vertex outside [blk_begin, blk_end) goes on bnd[]; a small
+  // fan-out kernel then copies the requests into EVERY rank's inbox and the circumcentres of the
+  // listed triangles to the ranks that own their vertices (launch_kernels.cuh), so that after a
+  // barrier all ranks apply the same requests and run the same flip rounds.
+  int t_begin;
+  int sharded;
+  int *req, *bnd;
+  int blk_begin, blk_end;      // cells of this rank
 };
 
 // Filtered-then-exact, kernel level.  K<false> bodies evaluate only the fp64 filters (no
@@ -141,10 +153,20 @@ FM_HD inline P3 ldv(const DtCtx& c, int i, int& id) {
 FM_HD inline P3 circumcentre(const P3& a, const P3& b, const P3& c, bool& degenerate) {
   double e3x = b.x - a.x, e3y = b.y - a.y, e3z = b.z - a.z;
   double e2x = c.x - a.x, e2y = c.y - a.y, e2z = c.z - a.z;
-  double nx = e3y * e2z - e3z * e2y;  // cross_product, src/math_mod.F90:12-22
+  // cross_product, src/math_mod.F90:12-22.  On the device the multiply-adds are spelled out so
+  // that every kernel that calls this (sweep, flip, circumcentre) rounds identically, whatever
+  // the compiler would contract: ranks of a sharded mesh then hold bit-identical circumcentres.
+#if defined(__CUDA_ARCH__)
+  double nx = __fma_rn(e3y, e2z, -__dmul_rn(e3z, e2y));
+  double ny = __fma_rn(e3z, e2x, -__dmul_rn(e3x, e2z));
+  double nz = __fma_rn(e3x, e2y, -__dmul_rn(e3y, e2x));
+  double l = sqrt(__fma_rn(nx, nx, __fma_rn(ny, ny, __dmul_rn(nz, nz))));
+#else
+  double nx = e3y * e2z - e3z * e2y;
   double ny = e3z * e2x - e3x * e2z;
   double nz = e3x * e2y - e3y * e2x;
   double l = sqrt(nx * nx + ny * ny + nz * nz);
+#endif
   degenerate = l < 2.220446049250313e-16;  // "collinear", DV:1339-1341
   if (degenerate) l = 1.0;
   return P3{nx / l, ny / l, nz / l};
@@ -362,7 +384,8 @@ typedef KCheckT<true> KCheck;
 // flip_check over T + circumcentre: the three vertices are gathered once.
 template <bool EXACT>
 struct KSweepT {
-  FM_HD static void run(const DtCtx& c, int t) {
+  FM_HD static void run(const DtCtx& c, int item) {
+    const int t = c.t_begin + item;
     Row r = c.row[t];
     I4 v = r.v, a = r.a;
     // stage 1: everything that depends only on the two rows -- three vertex records and the
@@ -398,9 +421,11 @@ struct KSweepT {
       if (s > 0) fe = 2;
       unsure = !EXACT && s == 0;
     }
-    if (unsure) { defer_item(c, t); return; }
+    if (unsure) { defer_item(c, item); return; }
     if (so < 0) FM_ATOMIC_ADD32(&c.counters[3], 1);
-    if (fe >= 0) {
+    if (fe >= 0 && c.sharded) {
+      c.req[FM_ATOMIC_ADD32(&c.counters[FM_C_REQ], 1)] = (t << 2) | fe;
+    } else if (fe >= 0) {
       c.flip_edge[t] = fe;
       u64 key = vote_key(c.stamp, t);
       FM_ATOMIC_MIN64(&c.vote[t], key);
@@ -412,6 +437,12 @@ struct KSweepT {
       P3 cc = circumcentre(pa, pb, pc, dg);
       if (dg) *c.err |= FM_E_TOPOLOGY;
       c.cc[t] = P4{cc.x, cc.y, cc.z, 0};
+      if (c.sharded) {
+        int lo = v.x < v.y ? (v.x < v.z ? v.x : v.z) : (v.y < v.z ? v.y : v.z);
+        int hi = v.x > v.y ? (v.x > v.z ? v.x : v.z) : (v.y > v.z ? v.y : v.z);
+        if (lo < c.blk_begin || hi >= c.blk_end)  // a vertex lives on another rank
+          c.bnd[FM_ATOMIC_ADD32(&c.counters[FM_C_BND], 1)] = t;
+      }
     }
   }
 };

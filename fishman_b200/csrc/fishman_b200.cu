@@ -98,6 +98,11 @@ struct fm_handle {
   // and mapped by the other ranks of the mesh (fm_peer_handle / fm_peer_attach)
   char* arena = nullptr;
   PeerSync* psync = nullptr;
+  int* inbox = nullptr;       // size regions of inbox_cap flip requests, one per sending rank
+  int* bnd = nullptr;         // swept triangles with a vertex on another rank (inbox_cap entries)
+  int inbox_cap = 0;
+  size_t off_sync = 0, off_inbox = 0, off_cc = 0;  // arena layout (the same on every rank)
+  int sweep_begin = 0, sweep_end = 0;              // triangle slots this rank sweeps (sharded warm repair)
   void* peer_base[8] = {nullptr};
   PeerCtx peer_ctx = {};
   bool peers_attached = false;
@@ -373,16 +378,24 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   A(cudaEventCreate(&h->ev0)); A(cudaEventCreate(&h->ev1));
   A(cudaMallocHost((void**)&h->pinned, 64 * sizeof(int)));
-  {  // arena = generator records + PeerSync block (exported as one IPC allocation)
-    size_t pts_bytes = sizeof(P4) * (size_t)h->n_pad;
-    A(cudaMalloc((void**)&h->arena, pts_bytes + sizeof(PeerSync)));
+  {  // arena = everything a peer rank touches (exported as ONE IPC allocation): generator records,
+     // PeerSync block, flip-request inbox, circumcentres
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    h->inbox_cap = size > 1 ? (int)((2 * T + size - 1) / size) + 64 : 0;
+    h->off_sync = up(sizeof(P4) * (size_t)h->n_pad);
+    h->off_inbox = up(h->off_sync + sizeof(PeerSync));
+    h->off_cc = up(h->off_inbox + sizeof(int) * (size_t)h->inbox_cap * size);
+    A(cudaMalloc((void**)&h->arena, h->off_cc + sizeof(P4) * T));
     h->pts = (P4*)h->arena;
-    h->psync = (PeerSync*)(h->arena + pts_bytes);
+    h->psync = (PeerSync*)(h->arena + h->off_sync);
+    h->inbox = (int*)(h->arena + h->off_inbox);
+    h->cc = (P4*)(h->arena + h->off_cc);
     A(cudaMemsetAsync(h->psync, 0, sizeof(PeerSync), h->stream));
+    A(dalloc(&h->bnd, (size_t)h->inbox_cap));
   }
   A(dalloc(&h->orig, n)); A(dalloc(&h->inv, n)); A(dalloc(&h->v2t, n));
   A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n));
-  A(dalloc(&h->rows, T)); A(dalloc(&h->cc, T));
+  A(dalloc(&h->rows, T));
   A(dalloc(&h->loc, n)); A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T));
   A(dalloc(&h->counters, 16));
@@ -488,9 +501,9 @@ extern "C" void fm_destroy(fm_handle* h) {
     for (void* p : mptrs)
       if (p) cudaFree(p);
   }
-  void* ptrs[] = {h->arena, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
+  void* ptrs[] = {h->arena, h->bnd, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->counters, h->winner, h->vote,
-                  h->mailbox, h->scratch64, h->cub_tmp, h->cc, h->cclon, h->cclat,
+                  h->mailbox, h->scratch64, h->cub_tmp, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -593,6 +606,22 @@ static int triangulate_cold(fm_handle* h) {
   h->n_tri = c.n_tri;
   if (h->n_tri != 2 * h->n - 4) { h->fail("triangle count %d != 2N-4", h->n_tri); return 1; }
   if (sort_triangles(h)) return 1;
+  h->sweep_begin = 0; h->sweep_end = h->n_tri;
+  if (h->size > 1) {  // the slots that go with this rank's cells (slots are sorted by smallest vertex now)
+    fm_tri_range<<<1, 32, 0, h->stream>>>(h->n_tri, h->rows, h->n_pad / h->size, h->size, h->rankbuf);
+    int rg[9] = {0};
+    FM_CUDA(cudaMemcpyAsync(rg, h->rankbuf, sizeof(int) * (h->size + 1), cudaMemcpyDeviceToHost, h->stream));
+    FM_CUDA(cudaStreamSynchronize(h->stream));
+    h->sweep_begin = rg[h->rank]; h->sweep_end = rg[h->rank + 1];
+    h->n_launch++;
+    bool fits = true;  // decided from ALL ranks' ranges, so that every rank decides the same
+    for (int k = 0; k < h->size; k++) fits = fits && (rg[k + 1] - rg[k] <= h->inbox_cap);
+    if (!fits) {  // a very uneven point set: equal parts instead
+      h->sweep_begin = (int)((long long)h->n_tri * h->rank / h->size);
+      h->sweep_end = (int)((long long)h->n_tri * (h->rank + 1) / h->size);
+    }
+    if (h->warm_graph) { cudaGraphExecDestroy(h->warm_graph); h->warm_graph = nullptr; }  // the range is baked in
+  }
   Readback r;
   if (readback(h, &r, "delaunay_triangulation")) return 1;
   account(h, r, st.rounds);
@@ -602,12 +631,51 @@ static int triangulate_cold(fm_handle* h) {
 }
 
 // warm repair of the existing connectivity, launches only; the caller reads counters[3]
-static int repair_async(fm_handle* h) {
+static void launch_peer_barrier(fm_handle* h, int phase);
+// sharded: (Lloyd loop on a mesh with attached peers) each rank sweeps its own triangle slots and
+// sends what it finds to all ranks; barrier; every rank applies all requests and runs the same
+// flip rounds.  Every rank must call this in step.
+static int repair_async(fm_handle* h, bool sharded = false) {
   CudaBackend be{h};
   DtCtx c = h->dt_ctx();
   c.cc = h->cc;
   DtStats st;
-  int rc = dt_repair_async(be, c, h->listA, h->listB, &h->stamp, &st, h->errmsg, sizeof h->errmsg);
+  if (!sharded) {
+    int rc = dt_repair_async(be, c, h->listA, h->listB, &h->stamp, &st, h->errmsg, sizeof h->errmsg);
+    return (h->cuda_failed || rc) ? 1 : 0;
+  }
+  int zero[15] = {0};
+  int* list[2] = {h->listA, h->listB};
+  be.write_ints(c.counters, zero, 15);
+  c.stamp = h->stamp;
+  c.next_active = list[0];
+  c.qcount = c.counters;
+  DtCtx cs = c;  // the sweep's view: its own range; findings go on the request / boundary lists
+  FanCtx f = {};
+  cs.t_begin = h->sweep_begin;
+  cs.sharded = 1;
+  f.blk_per = h->n_pad / h->size;
+  cs.blk_begin = h->blk_begin; cs.blk_end = h->blk_begin + f.blk_per;
+  for (int k = 0; k < h->size; k++) {
+    char* base = (k == h->rank) ? h->arena : (char*)h->peer_base[k];
+    f.inbox[k] = (int*)(base + h->off_inbox) + (size_t)h->rank * h->inbox_cap;
+    f.cc[k] = (P4*)(base + h->off_cc);
+  }
+  cs.req = f.inbox[h->rank];  // this rank's own region of its own inbox
+  cs.bnd = h->bnd;
+  f.row = h->rows; f.req = cs.req; f.bnd = h->bnd; f.counters = h->counters;
+  f.rank = h->rank; f.size = h->size;
+  be.launch_filtered<KSweepT>(cs, h->sweep_end - h->sweep_begin);
+  h->prof_begin();
+  fm_sweep_fanout<<<h->sms, 256, 0, h->stream>>>(f);
+  h->note_cuda(cudaGetLastError(), "sweep_fanout");
+  h->prof_end("sweep_fanout", 0);
+  launch_peer_barrier(h, 2);
+  h->prof_begin();
+  fm_apply_requests<<<h->sms * 2, 256, 0, h->stream>>>(c, h->peer_ctx, h->inbox, h->inbox_cap);
+  h->note_cuda(cudaGetLastError(), "apply_requests");
+  h->prof_end("apply_requests", 0);
+  int rc = be.flip_loop(c, list, 0, true, &h->stamp, &st, h->errmsg, sizeof h->errmsg, -1);
   return (h->cuda_failed || rc) ? 1 : 0;
 }
 
@@ -913,7 +981,7 @@ static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
       cudaError_t e = cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal);
       bool ok = (e == cudaSuccess);
       if (ok) {
-        int rc = repair_async(h);
+        int rc = repair_async(h, h->peers_attached);
         launch_centroid(h, rho, true);
         cudaError_t e2 = readback_enqueue(h);
         e = cudaStreamEndCapture(h->stream, &g);
@@ -936,13 +1004,13 @@ static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
       }
     }
     if (h->warm_graph) {
-      h->n_launch += h->peers_attached ? 6 : 4;  // sweep, deferred sweep, flip loop, centroid (+ 2 barriers)
+      h->n_launch += h->peers_attached ? 9 : 4;  // sweep, deferred sweep, flip loop, centroid (+ fan-out, 3 barriers, apply)
       cudaError_t e = cudaGraphLaunch(h->warm_graph, h->stream);
       if (e != cudaSuccess) { h->fail("cudaGraphLaunch: %s", cudaGetErrorString(e)); return 1; }
       return 0;
     }
   }
-  if (repair_async(h)) return 1;
+  if (repair_async(h, h->peers_attached)) return 1;
   launch_centroid(h, rho, true);
   cudaError_t e = readback_enqueue(h);
   if (e != cudaSuccess) { h->fail("readback: %s", cudaGetErrorString(e)); return 1; }
@@ -1012,7 +1080,6 @@ extern "C" int fm_peer_attach(fm_handle* h, const void* handles) {
   if (h->size < 2 || h->size > 8) { h->fail("fm_peer_attach: size must be 2..8, got %d", h->size); return 1; }
   if (h->peers_attached) { h->fail("fm_peer_attach: already attached"); return 1; }
   FM_CUDA(h->sync());
-  size_t pts_bytes = sizeof(P4) * (size_t)h->n_pad;
   PeerCtx pc = {};
   pc.rank = h->rank; pc.size = h->size;
   for (int k = 0; k < h->size; k++) {
@@ -1020,7 +1087,7 @@ extern "C" int fm_peer_attach(fm_handle* h, const void* handles) {
     cudaIpcMemHandle_t hd;
     memcpy(&hd, (const char*)handles + 64 * (size_t)k, sizeof hd);
     FM_CUDA(cudaIpcOpenMemHandle(&h->peer_base[k], hd, cudaIpcMemLazyEnablePeerAccess));
-    pc.sync[k] = (PeerSync*)((char*)h->peer_base[k] + pts_bytes);
+    pc.sync[k] = (PeerSync*)((char*)h->peer_base[k] + h->off_sync);
   }
   h->peer_ctx = pc;
   h->peers_attached = true;

@@ -129,20 +129,25 @@ __global__ void __launch_bounds__(128, FM_OCC_CENTROID) fm_centroid_update(const
 //   flag[k]      written by rank k: the last barrier epoch rank k has reached
 //   epoch        local: barriers executed so far (every rank executes the same sequence)
 //   maxdisp_all  bits of the largest chord displacement over ALL ranks of the current iteration
+//   req_count[k] flip requests rank k put into this rank's inbox (sharded sweep), bad[k] = the
+//                turned-over triangles rank k counted in its part of the sweep
 struct PeerSync {
   int flag[8];
   int epoch;
   int pad[7];
   u64 maxdisp_all;
   u64 pad2[7];
+  int req_count[8];
+  int bad[8];
 };
 struct PeerCtx {
   PeerSync* sync[8];  // by rank; sync[rank] is the local block
   int rank, size;
 };
-// phase 0 (before the centroid kernel: every rank has finished reading the generators) and
+// phase 0 (before the centroid kernel: every rank has finished reading the generators),
 // phase 1 (after it: every rank's stores into this rank's generator array have landed, and the
-// displacement maxima have been combined).  One warp; lane k talks to rank k.  A rank that does
+// displacement maxima have been combined) and phase 2 (after a sharded sweep: every rank's flip
+// requests and circumcentres have landed here, and their counts are known).  One warp; lane k talks to rank k.  A rank that does
 // not show up within ~2 s of SM clocks sets FM_E_PEER instead of hanging the device.
 __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
   __shared__ int ep;
@@ -160,6 +165,10 @@ __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
       u64 mine = *(volatile u64*)(counters + FM_C_MAXDISP);
       atomicMax_system((unsigned long long*)&pc.sync[k]->maxdisp_all, (unsigned long long)mine);
     }
+    if (phase == 2) {
+      *(volatile int*)&pc.sync[k]->req_count[pc.rank] = *(volatile int*)(counters + FM_C_REQ);
+      *(volatile int*)&pc.sync[k]->bad[pc.rank] = *(volatile int*)(counters + 3);
+    }
     __threadfence_system();
     *(volatile int*)&pc.sync[k]->flag[pc.rank] = e;
     long long t0 = clock64();
@@ -172,6 +181,80 @@ __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
     __threadfence_system();
     *(volatile u64*)(counters + FM_C_MAXDISP) = *(volatile u64*)&self->maxdisp_all;
   }
+}
+
+// Fan-out of a sharded sweep's findings over NVLink: the flip requests to every rank's inbox
+// (region `rank`), the circumcentres of the listed boundary triangles to the owners of their
+// vertices.  Small: a few thousand requests and O(sqrt N) boundary triangles per iteration.
+struct FanCtx {
+  int* inbox[8];   // by rank: this rank's region of that rank's inbox ([rank] = req itself)
+  P4* cc[8];       // by rank: circumcentre arrays
+  const Row* row;
+  const int *req, *bnd;
+  const int* counters;
+  int rank, size, blk_per;
+};
+__global__ void __launch_bounds__(256) fm_sweep_fanout(FanCtx f) {
+  const int gsz = gridDim.x * blockDim.x, gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nreq = f.counters[FM_C_REQ], nbnd = f.counters[FM_C_BND];
+  for (int i = gid; i < nreq; i += gsz) {
+    int msg = f.req[i];
+    for (int k = 0; k < f.size; k++)
+      if (k != f.rank) f.inbox[k][i] = msg;
+  }
+  for (int i = gid; i < nbnd; i += gsz) {
+    int t = f.bnd[i];
+    I4 v = f.row[t].v;
+    P4 rec = f.cc[f.rank][t];
+    int o0 = v.x / f.blk_per, o1 = v.y / f.blk_per, o2 = v.z / f.blk_per;
+    if (o0 != f.rank) f.cc[o0][t] = rec;
+    if (o1 != f.rank && o1 != o0) f.cc[o1][t] = rec;
+    if (o2 != f.rank && o2 != o0 && o2 != o1) f.cc[o2][t] = rec;
+  }
+}
+
+// After a sharded sweep and its barrier: every rank turns ALL requests (its own and its peers')
+// into what the unsharded sweep does on the spot -- the wanted edge, the two votes, the queue
+// entry -- and adds up the turned-over counts.  Votes are atomicMin and the flip rounds depend
+// only on the SET of queued triangles, so every rank goes on to the same flips.
+__global__ void __launch_bounds__(256) fm_apply_requests(DtCtx c, PeerCtx pc, const int* inbox, int cap) {
+  use_device_stamp(c);
+  const PeerSync* self = pc.sync[pc.rank];
+  const int gsz = gridDim.x * blockDim.x, gid = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int k = 0; k < pc.size; k++) {
+    int cnt = *(volatile const int*)&self->req_count[k];
+    if (cnt > cap) { if (gid == 0) atomicOr(c.err, FM_E_OVERFLOW); cnt = cap; }
+    const int* box = inbox + (size_t)k * cap;
+    for (int i = gid; i < cnt; i += gsz) {
+      int msg = box[i], t = msg >> 2, fe = msg & 3;
+      c.flip_edge[t] = fe;
+      u64 key = vote_key(c.stamp, t);
+      atomicMin((unsigned long long*)&c.vote[t], key);
+      atomicMin((unsigned long long*)&c.vote[geti(c.row[t].a, fe) >> 2], key);
+      queue_active(c, t, c.stamp);
+    }
+  }
+  if (gid == 0) {
+    int bad = 0;
+    for (int k = 0; k < pc.size; k++) bad += *(volatile const int*)&self->bad[k];
+    c.counters[3] = bad;
+  }
+}
+
+// out[r] = first triangle slot whose smallest vertex is >= r * per, r = 0 .. size (slots are
+// sorted by that key right after a cold build): rank r sweeps the slots [out[r], out[r+1]), the
+// ones that go with its cells
+__global__ void fm_tri_range(int nt, const Row* row, int per, int size, int* out) {
+  int r = threadIdx.x;
+  if (r > size) return;
+  long long key = (long long)r * per;
+  int a = 0, b = nt;
+  while (a < b) {
+    int mid = (a + b) >> 1;
+    I4 v = row[mid].v;
+    if (min(v.x, min(v.y, v.z)) < key) a = mid + 1; else b = mid;
+  }
+  out[r] = (r == size) ? nt : a;
 }
 
 // ---- spatial renumbering of the triangle slots (after a cold build)

@@ -32,12 +32,18 @@ def main():
     ref = fb.Mesh.from_xyz(p)
     md_ref = [ref.lloyd(rho, max_iter=1, warm=True)[1] for _ in range(iters)]
     g_ref = ref.generators()
+    st_ref = ref.stats()
+    ref.retriangulate(warm=False)
+    tri_ref = fb.canonical_triangles(ref.triangles()[0])
     ref.close()
 
     a = fb.Mesh.from_xyz(p, rank=rank, size=world)
     a.peer_connect(dist)
     md_a = [a.lloyd(rho, max_iter=1, warm=True)[1] for _ in range(iters)]
     g_a = a.generators()
+    st_a = a.stats()
+    a.retriangulate(warm=False)
+    tri_a = fb.canonical_triangles(a.triangles()[0])
     a.close()
 
     b = fb.Mesh.from_xyz(p, rank=rank, size=world)
@@ -55,6 +61,12 @@ def main():
     print(f"rank {rank}/{world}: n={n} iters={iters} p2p==single {np.array_equal(g_ref, g_a)} "
           f"nccl==single {np.array_equal(g_ref, g_b)} maxdisp equal {md_ref == md_a and md_ref == md_b} "
           f"last maxdisp {md_ref[-1]:.3e}", flush=True)
+    if not np.array_equal(g_ref, g_a):
+        d = np.abs(g_ref - g_a).max(1)
+        print(f"rank {rank}: p2p differs from single in {int((d > 0).sum())} generators, max {d.max():.3e}; "
+              f"flips single {st_ref['flips']} p2p {st_a['flips']}; final topology equal "
+              f"{np.array_equal(tri_ref, tri_a)}; first maxdisp mismatch at "
+              f"{next((i for i, (x, y) in enumerate(zip(md_ref, md_a)) if x != y), None)}", flush=True)
     t = torch.tensor([0 if ok else 1], device=f"cuda:{local}")
     dist.all_reduce(t)
     dist.destroy_process_group()
