@@ -122,7 +122,6 @@ struct DtCtx {
   // listed triangles to the ranks that own their vertices (launch_kernels.cuh), so that after a
   // barrier all ranks apply the same requests and run the same flip rounds.
   int t_begin;
-  int sharded;
   int *req, *bnd;
   int blk_begin, blk_end;      // cells of this rank
 };
@@ -382,10 +381,10 @@ typedef KCheckT<true> KCheck;
 // KCheck does, queueing the claimant for the mark/flip/patch phases, and (c) refreshes the
 // circumcentre of every triangle (flips refresh theirs).  Replaces validate + queue_all +
 // flip_check over T + circumcentre: the three vertices are gathered once.
-template <bool EXACT>
-struct KSweepT {
+template <bool EXACT, bool SHARDED>
+struct KSweepImpl {
   FM_HD static void run(const DtCtx& c, int item) {
-    const int t = c.t_begin + item;
+    const int t = SHARDED ? c.t_begin + item : item;
     Row r = c.row[t];
     I4 v = r.v, a = r.a;
     // stage 1: everything that depends only on the two rows -- three vertex records and the
@@ -423,7 +422,7 @@ struct KSweepT {
     }
     if (unsure) { defer_item(c, item); return; }
     if (so < 0) FM_ATOMIC_ADD32(&c.counters[3], 1);
-    if (fe >= 0 && c.sharded) {
+    if (fe >= 0 && SHARDED) {
       c.req[FM_ATOMIC_ADD32(&c.counters[FM_C_REQ], 1)] = (t << 2) | fe;
     } else if (fe >= 0) {
       c.flip_edge[t] = fe;
@@ -437,7 +436,7 @@ struct KSweepT {
       P3 cc = circumcentre(pa, pb, pc, dg);
       if (dg) *c.err |= FM_E_TOPOLOGY;
       c.cc[t] = P4{cc.x, cc.y, cc.z, 0};
-      if (c.sharded) {
+      if (SHARDED) {
         int lo = v.x < v.y ? (v.x < v.z ? v.x : v.z) : (v.y < v.z ? v.y : v.z);
         int hi = v.x > v.y ? (v.x > v.z ? v.x : v.z) : (v.y > v.z ? v.y : v.z);
         if (lo < c.blk_begin || hi >= c.blk_end)  // a vertex lives on another rank
@@ -446,6 +445,8 @@ struct KSweepT {
     }
   }
 };
+template <bool EXACT> struct KSweepT : KSweepImpl<EXACT, false> {};    // the whole mesh
+template <bool EXACT> struct KSweepShT : KSweepImpl<EXACT, true> {};   // this rank's slots of a sharded mesh
 typedef KSweepT<true> KSweep;
 
 struct KMark {

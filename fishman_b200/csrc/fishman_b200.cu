@@ -40,6 +40,8 @@ FM_KNAME(KFlip, "flip22")
 FM_KNAME(KPatch, "flip_patch")
 FM_KNAME(KSweep, "sweep_exact")
 FM_KNAME(KSweepT<false>, "sweep")
+FM_KNAME(KSweepShT<true>, "sweep_exact")
+FM_KNAME(KSweepShT<false>, "sweep")
 FM_KNAME(KValidate, "validate")
 FM_KNAME(KCircum, "circumcentre")
 FM_KNAME(KDegree, "ring_degree")
@@ -653,7 +655,6 @@ static int repair_async(fm_handle* h, bool sharded = false) {
   DtCtx cs = c;  // the sweep's view: its own range; findings go on the request / boundary lists
   FanCtx f = {};
   cs.t_begin = h->sweep_begin;
-  cs.sharded = 1;
   f.blk_per = h->n_pad / h->size;
   cs.blk_begin = h->blk_begin; cs.blk_end = h->blk_begin + f.blk_per;
   for (int k = 0; k < h->size; k++) {
@@ -665,7 +666,7 @@ static int repair_async(fm_handle* h, bool sharded = false) {
   cs.bnd = h->bnd;
   f.row = h->rows; f.req = cs.req; f.bnd = h->bnd; f.counters = h->counters;
   f.rank = h->rank; f.size = h->size;
-  be.launch_filtered<KSweepT>(cs, h->sweep_end - h->sweep_begin);
+  be.launch_filtered<KSweepShT>(cs, h->sweep_end - h->sweep_begin);
   h->prof_begin();
   fm_sweep_fanout<<<h->sms, 256, 0, h->stream>>>(f);
   h->note_cuda(cudaGetLastError(), "sweep_fanout");

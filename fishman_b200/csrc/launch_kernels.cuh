@@ -21,6 +21,7 @@ __device__ __forceinline__ void use_device_stamp(VdCtx&) {}
 // fit 64 registers without spilling, so four blocks hide the gather latency.
 template <class K> struct KOcc { static const int value = 1; };
 template <> struct KOcc<KSweepT<false>> { static const int value = 4; };
+template <> struct KOcc<KSweepShT<false>> { static const int value = 4; };
 template <> struct KOcc<KLocateVoteT<false>> { static const int value = 4; };
 template <> struct KOcc<KCheckT<false>> { static const int value = 4; };
 
