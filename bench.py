@@ -42,6 +42,19 @@ ALG_BYTES = {
 }
 
 
+def ncu_extra(kernel, n):
+    """fp64-pipe and DRAM utilisation of `kernel` from the same committed capture (informational:
+    the centroid kernel sits nearer its fp64-pipe bound than its HBM bound)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        k = t["kernels"][kernel]
+        return {"fp64_pipe_pct": k.get("fp64_pipe_pct"), "dram_pct_of_peak": k.get("dram_pct_of_peak"),
+                "source": t["source"]} if t["generators"] == n else None
+    except Exception:
+        return None
+
+
 def ncu_traffic(kernel, n):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed
     ncu --set full capture (profiles/traffic.json), valid for the generator count it was taken at."""
@@ -203,6 +216,8 @@ def run_gpu(args):
     rho = fb.density_uniform()
     m = fb.Mesh.from_xyz(p, rank=rank, size=world)
     gather = None
+    if world > 1 and args.exchange == "p2p" and torch.cuda.device_count() < world:
+        args.exchange = "nccl"   # ranks sharing a GPU: the peer exchange needs one GPU per rank
     if world > 1 and args.exchange == "p2p":
         m.peer_connect(dist)   # the Lloyd kernel stores into every rank's generator array over NVLink
     elif world > 1:
@@ -307,7 +322,8 @@ def run_gpu(args):
                          "profiled_pass_ms_per_step": ms_prof / args.steps,
                          "alg_bytes_per_item": ALG_BYTES.get(top["name"], 0),
                          "items_per_launch": top["threads"] / max(top["launches"], 1),
-                         "avg_launch_ms": dur_ms, "share_of_step": top["ms"] / tot},
+                         "avg_launch_ms": dur_ms, "share_of_step": top["ms"] / tot,
+                         "ncu": ncu_extra(top["name"], n)},
             "kernels": [{"name": r["name"], "launches": r["launches"], "ms": round(r["ms"], 4),
                          "share": round(r["ms"] / tot, 4)} for r in rows],
             "dt_stats": {k: st[k] for k in ("rounds", "subrounds", "flips", "max_active", "cold", "warm")},

@@ -377,6 +377,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   h->coop_blocks = sms * (per_sm > 0 ? per_sm : 1);
   if (const char* e = getenv("FM_COOP_BLOCKS")) { int v = atoi(e); if (v > 0 && v <= h->coop_blocks) h->coop_blocks = v; }
   h->sms = sms;
+  if (getenv("FM_NO_GRAPH")) h->graph_disabled = true;  // direct launches (profilers that do not follow graphs)
   A(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   A(cudaEventCreate(&h->ev0)); A(cudaEventCreate(&h->ev1));
   A(cudaMallocHost((void**)&h->pinned, 64 * sizeof(int)));
@@ -1070,23 +1071,42 @@ extern "C" int fm_lloyd(fm_handle* h, const fm_density* rho, int32_t max_iter, d
 }
 
 // ---- peer exchange over NVLink (CUDA IPC between the processes of one box)
-extern "C" int fm_peer_handle(fm_handle* h, void* out64) {
+// handle blob = 64-byte CUDA IPC handle + 16-byte UUID of the device the rank runs on
+static int device_uuid(fm_handle* h, char* out16) {
+  int dev = 0;
+  cudaDeviceProp p;
+  FM_CUDA(cudaGetDevice(&dev));
+  FM_CUDA(cudaGetDeviceProperties(&p, dev));
+  memcpy(out16, &p.uuid, 16);
+  return 0;
+}
+extern "C" int fm_peer_handle(fm_handle* h, void* out80) {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
   cudaIpcMemHandle_t hd;
   FM_CUDA(cudaIpcGetMemHandle(&hd, h->arena));
-  memcpy(out64, &hd, sizeof hd);
-  return 0;
+  memcpy(out80, &hd, sizeof hd);
+  return device_uuid(h, (char*)out80 + 64);
 }
 extern "C" int fm_peer_attach(fm_handle* h, const void* handles) {
   if (h->size < 2 || h->size > 8) { h->fail("fm_peer_attach: size must be 2..8, got %d", h->size); return 1; }
   if (h->peers_attached) { h->fail("fm_peer_attach: already attached"); return 1; }
   FM_CUDA(h->sync());
+  char mine[16];
+  if (device_uuid(h, mine)) return 1;
+  for (int k = 0; k < h->size; k++)
+    if (k != h->rank && memcmp(mine, (const char*)handles + 80 * (size_t)k + 64, 16) == 0) {
+      // the barrier kernels of two ranks would wait on each other on ONE device, where nothing
+      // guarantees that they run at the same time
+      h->fail("fm_peer_attach: ranks %d and %d run on the same GPU; the peer exchange needs one GPU per rank "
+              "(use fm_lloyd_local + an all-gather instead)", h->rank, k);
+      return 1;
+    }
   PeerCtx pc = {};
   pc.rank = h->rank; pc.size = h->size;
   for (int k = 0; k < h->size; k++) {
     if (k == h->rank) { pc.sync[k] = h->psync; continue; }
     cudaIpcMemHandle_t hd;
-    memcpy(&hd, (const char*)handles + 64 * (size_t)k, sizeof hd);
+    memcpy(&hd, (const char*)handles + 80 * (size_t)k, sizeof hd);
     FM_CUDA(cudaIpcOpenMemHandle(&h->peer_base[k], hd, cudaIpcMemLazyEnablePeerAccess));
     pc.sync[k] = (PeerSync*)((char*)h->peer_base[k] + h->off_sync);
   }

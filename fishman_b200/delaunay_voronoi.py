@@ -234,8 +234,8 @@ class Mesh:
     def peer_connect(self, dist):
         """Maps the generator arrays of all ranks into each other (fm_peer_handle /
         fm_peer_attach); `dist` is an initialised torch.distributed, used only to pass the
-        64-byte IPC handles around.  Afterwards lloyd() runs on the sharded mesh."""
-        buf = C.create_string_buffer(64)
+        80-byte handle blobs around.  Afterwards lloyd() runs on the sharded mesh."""
+        buf = C.create_string_buffer(80)
         self._chk(_lib.lib().fm_peer_handle(self._h, buf))
         got = [None] * self.size
         dist.all_gather_object(got, buf.raw)

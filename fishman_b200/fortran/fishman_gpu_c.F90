@@ -181,11 +181,11 @@ module fishman_gpu_c
       integer(c_int64_t), intent(out) :: n_padded, begin, count
     end function fm_generator_block
 
-    ! 64-byte CUDA IPC handle of this rank; exchange with MPI_Allgather, then attach all of them
-    integer(c_int) function fm_peer_handle(h, out64) bind(C, name='fm_peer_handle')
+    ! 80-byte blob (CUDA IPC handle + device UUID) of this rank; exchange with MPI_Allgather, then attach all
+    integer(c_int) function fm_peer_handle(h, out80) bind(C, name='fm_peer_handle')
       import :: c_int, c_char, c_ptr
       type(c_ptr), value :: h
-      character(kind=c_char), intent(out) :: out64(64)
+      character(kind=c_char), intent(out) :: out80(80)
     end function fm_peer_handle
 
     integer(c_int) function fm_peer_attach(h, handles) bind(C, name='fm_peer_attach')

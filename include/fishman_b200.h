@@ -127,11 +127,15 @@ int fm_generator_block(fm_handle* h, void** d_records, int64_t* n_padded, int64_
 /* Peer exchange over NVLink (sharded handles, one process per GPU of one box): instead of a
  * collective after the Lloyd kernel, the kernel itself stores every updated generator into the
  * generator arrays of all ranks through CUDA IPC peer mappings, between two device-side barriers.
- * fm_peer_handle writes this rank's 64-byte IPC handle; the host exchanges the handles by
- * whatever means it has (MPI_Allgather, torch.distributed) and passes all `size` of them, in
- * rank order, to fm_peer_attach.  Afterwards fm_lloyd runs the whole loop on a sharded handle
+ * fm_peer_handle writes this rank's FM_PEER_HANDLE_BYTES-byte blob (CUDA IPC handle + device
+ * UUID); the host exchanges the blobs by whatever means it has (MPI_Allgather,
+ * torch.distributed) and passes all `size` of them, in rank order, to fm_peer_attach, which
+ * fails if two ranks share a GPU (one GPU per rank is required: the barrier kernels of the ranks
+ * wait on each other).  The warm sweep is then sharded as well: each rank tests the triangles of
+ * its own cells and sends the edges to flip to all ranks.  Afterwards fm_lloyd runs the whole loop on a sharded handle
  * (every rank calls it with the same arguments) and *max_disp is the maximum over all ranks. */
-int fm_peer_handle(fm_handle* h, void* out64);
+#define FM_PEER_HANDLE_BYTES 80
+int fm_peer_handle(fm_handle* h, void* out80);
 int fm_peer_attach(fm_handle* h, const void* handles);
 /* generators in input order (device -> host) */
 int fm_get_generators(fm_handle* h, double* x, double* y, double* z);
