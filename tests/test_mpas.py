@@ -159,3 +159,40 @@ def test_device_mpas_strict_error_and_order():
         mesh.mpas(strict=True)
     assert mesh.mpas(strict=False)["maxEdges"] >= 7
     mesh.close()
+
+
+def test_writer_contract_and_grids_roundtrip(tmp_path):
+    """The on-disk contract of mpas_mesh_output (MM:89-138): 37 variables over 7 sized dimensions;
+    the grids input contract of gen_mesh (vtx_p(location_nv, 3), src/gen_mesh.F90:16-22)."""
+    from fishman_b200 import mpas_mesh
+    assert len(mpas_mesh.VARIABLES) == 37 and len({v for v, _ in mpas_mesh.VARIABLES}) == 37
+    dims = {d for _, ds in mpas_mesh.VARIABLES for d in ds}
+    assert dims == {"nCells", "nEdges", "nVertices", "vertexDegree", "maxEdges", "maxEdges2", "TWO"}
+    p = points.ico(2)
+    f = str(tmp_path / "grids.npz")
+    mpas_mesh.write_grids(f, p)
+    assert np.array_equal(mpas_mesh.read_grids(f), p)
+
+
+@pytest.mark.gpu
+def test_gen_mesh_end_to_end(tmp_path):
+    """program gen_mesh: grids file -> DT -> VD(all) -> MPAS file, against the oracle's arrays."""
+    from fishman_b200 import mpas_mesh
+    p = points.ico(4)
+    f = str(tmp_path / "grids.npz")
+    mpas_mesh.write_grids(f, p)
+    out = mpas_mesh.gen_mesh(f, str(tmp_path / "mpas_mesh.2562.npz"))
+    d = np.load(out)
+    g, r = oracle_mpas(p)
+    sizes = {k[4:]: int(d[k]) for k in d.files if k.startswith("dim_")}
+    assert sizes == dict(nCells=2562, nEdges=7680, nVertices=5120, vertexDegree=3, maxEdges=6, maxEdges2=12, TWO=2)
+    assert str(d["att_on_a_sphere"]) == "YES" and float(d["att_sphere_radius"]) == 1.0
+    for name, ds in mpas_mesh.VARIABLES:
+        assert d[name].shape == tuple(sizes[x] for x in ds), name
+    for name in ("cellsOnEdge", "cellsOnCell", "edgesOnCell", "nEdgesOnCell", "nEdgesOnEdge", "edgesOnEdge"):
+        assert np.array_equal(d[name], r[name]), name
+    for name in ("dcEdge", "angleEdge", "areaCell"):
+        assert np.abs(d[name] - r[name]).max() < TOL, name
+    assert np.abs(np.stack([d["xEdge"], d["yEdge"], d["zEdge"]], 1) - r["xyzEdge"]).max() < TOL
+    assert np.abs(np.stack([d["xCell"], d["yCell"], d["zCell"]], 1) - p).max() == 0.0
+    assert np.abs(np.abs(d["weightsOnEdge"]) - np.abs(r["weightsOnEdge"])).max() < 1e-9
