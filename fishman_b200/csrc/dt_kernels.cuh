@@ -449,6 +449,19 @@ template <bool EXACT> struct KSweepT : KSweepImpl<EXACT, false> {};    // the wh
 template <bool EXACT> struct KSweepShT : KSweepImpl<EXACT, true> {};   // this rank's slots of a sharded mesh
 typedef KSweepT<true> KSweep;
 
+// Sharded sweep, second half (every rank, over ALL ranks' requests): what KSweep does on the spot
+// when it finds a violated edge -- the wanted edge, the two votes, the queue entry.
+struct KApply {
+  FM_HD static void run(const DtCtx& c, int msg) {
+    int t = msg >> 2, fe = msg & 3;
+    c.flip_edge[t] = fe;
+    u64 key = vote_key(c.stamp, t);
+    FM_ATOMIC_MIN64(&c.vote[t], key);
+    FM_ATOMIC_MIN64(&c.vote[geti(c.row[t].a, fe) >> 2], key);
+    queue_active(c, t, c.stamp);
+  }
+};
+
 struct KMark {
   FM_HD static void run(const DtCtx& c, int i) {
     int t = c.active[i];

@@ -226,14 +226,7 @@ __global__ void __launch_bounds__(256) fm_apply_requests(DtCtx c, PeerCtx pc, co
     int cnt = *(volatile const int*)&self->req_count[k];
     if (cnt > cap) { if (gid == 0) atomicOr(c.err, FM_E_OVERFLOW); cnt = cap; }
     const int* box = inbox + (size_t)k * cap;
-    for (int i = gid; i < cnt; i += gsz) {
-      int msg = box[i], t = msg >> 2, fe = msg & 3;
-      c.flip_edge[t] = fe;
-      u64 key = vote_key(c.stamp, t);
-      atomicMin((unsigned long long*)&c.vote[t], key);
-      atomicMin((unsigned long long*)&c.vote[geti(c.row[t].a, fe) >> 2], key);
-      queue_active(c, t, c.stamp);
-    }
+    for (int i = gid; i < cnt; i += gsz) KApply::run(c, box[i]);
   }
   if (gid == 0) {
     int bad = 0;

@@ -46,3 +46,22 @@ def triangulate(xyz, sort=True):
     if rc:
         raise RuntimeError(lib().fme_last_error().decode())
     return tri, adj, dict(rounds=int(st[0]), subrounds=int(st[1]), flips=int(st[2]), max_active=int(st[3]))
+
+
+def repair(xyz_old, xyz_new, nranks=1, reverse=False):
+    """Warm repair of the triangulation of xyz_old after the points moved to xyz_new, as `nranks`
+    ranks of a sharded mesh do it (nranks = 1: the unsharded sweep).  Returns (tri, adj, turned,
+    n_requests); tri/adj are slot-for-slot comparable between runs."""
+    a = np.ascontiguousarray(xyz_old, dtype=np.float64)
+    b = np.ascontiguousarray(xyz_new, dtype=np.float64)
+    n = len(a)
+    T = 2 * n - 4
+    tri = np.empty((T, 3), np.int32)
+    adj = np.empty((T, 3), np.int32)
+    turned, nreq = C.c_int(0), C.c_int(0)
+    ip, dp = C.POINTER(C.c_int), C.POINTER(C.c_double)
+    rc = lib().fme_repair(n, a.ctypes.data_as(dp), b.ctypes.data_as(dp), int(nranks), 1 if reverse else 0,
+                          tri.ctypes.data_as(ip), adj.ctypes.data_as(ip), C.byref(turned), C.byref(nreq))
+    if rc:
+        raise RuntimeError(lib().fme_last_error().decode())
+    return tri, adj, turned.value, nreq.value

@@ -71,56 +71,130 @@ static char g_err[512];
 
 extern "C" const char* fme_last_error() { return g_err; }
 
+// One mesh on the host: the arrays of the CUDA handle as std::vectors.
+struct EmuMesh {
+  int n = 0, T = 0, stamp = 1, err = 0;
+  int counters[16] = {0};
+  std::vector<int> orig, loc, rank, flip_edge, role, amark, listA, listB, v2t, slow;
+  std::vector<P4> pts;
+  std::vector<Row> row;
+  std::vector<u64> winner, vote, mailbox;
+  DtCtx c;
+  HostBackend be;
+  DtStats st;
+
+  int build(int n_, const double* xyz, int do_sort) {
+    n = n_; T = 2 * n - 4;
+    orig.resize(n);
+    std::iota(orig.begin(), orig.end(), 0);
+    if (do_sort) {
+      std::vector<u64> key(n);
+      for (int i = 0; i < n; i++) key[i] = morton_key(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+      std::stable_sort(orig.begin(), orig.end(), [&](int a, int b) { return key[a] < key[b]; });
+    }
+    pts.resize(n);
+    for (int i = 0; i < n; i++) pts[i] = P4{xyz[3 * orig[i]], xyz[3 * orig[i] + 1], xyz[3 * orig[i] + 2], orig[i]};
+    row.assign(T, Row());
+    loc.assign(n, 0); rank.assign(T + 1, 0); flip_edge.assign(T, 0); role.assign(T, 0); amark.assign(T, 0);
+    listA.assign(T, 0); listB.assign(T, 0); v2t.assign(n, -1); slow.assign(T + 1, 0);
+    winner.assign(T, 0); vote.assign(T, kNone64); mailbox.assign(3 * (size_t)T, 0);
+    memset(&c, 0, sizeof c);
+    c.n = n; c.pts = pts.data(); c.v2t = v2t.data();
+    c.row = row.data(); c.loc = loc.data(); c.winner = winner.data();
+    c.rank = rank.data(); c.vote = vote.data(); c.flip_edge = flip_edge.data(); c.role = role.data();
+    c.mailbox = mailbox.data(); c.amark = amark.data(); c.counters = counters; c.err = &err; c.slow = slow.data();
+    int boot[4];
+    if (dt_bootstrap(be, c, boot, g_err, sizeof g_err)) return 1;
+    for (int k = 0; k < 4; k++) loc[boot[k]] = -1;
+    int K = dt_level_count(n);
+    std::vector<int> order(n), off(K + 2, 0), prev(n);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+      return point_class(pts[a].id, K) > point_class(pts[b].id, K);  // level = K - class, ascending
+    });
+    for (int i = 0; i < n; i++) off[K - point_class(pts[i].id, K) + 1]++;
+    for (int L = 0; L <= K; L++) off[L + 1] += off[L];
+    if (dt_run(be, c, listA.data(), listB.data(), order.data(), off.data(), K, prev.data(), boot, &stamp, &st,
+               g_err, sizeof g_err))
+      return 1;
+    if (c.n_tri != T) { snprintf(g_err, sizeof g_err, "triangle count %d != 2n-4", c.n_tri); return 1; }
+    return 0;
+  }
+  void export_tris(int* tri_out, int* adj_out) {
+    for (int t = 0; t < T; t++)
+      for (int k = 0; k < 3; k++) {
+        tri_out[3 * t + k] = orig[geti(row[t].v, k)] + 1;
+        adj_out[3 * t + k] = (geti(row[t].a, k) >> 2) + 1;
+      }
+  }
+};
+
 // xyz: n x 3 row major.  tri/adj: (2n-4) x 3, 1-based ORIGINAL ids / triangle ids.
 // stats: rounds, subrounds, flips, max_active.
 extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_out, int* stats,
                                int do_sort) {
   g_err[0] = 0;
   if (n < 4) { snprintf(g_err, sizeof g_err, "need at least 4 points"); return 1; }
-  std::vector<int> orig(n);
-  std::iota(orig.begin(), orig.end(), 0);
-  if (do_sort) {
-    std::vector<u64> key(n);
-    for (int i = 0; i < n; i++) key[i] = morton_key(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
-    std::stable_sort(orig.begin(), orig.end(), [&](int a, int b) { return key[a] < key[b]; });
+  EmuMesh m;
+  if (m.build(n, xyz, do_sort)) return 1;
+  m.export_tris(tri_out, adj_out);
+  if (stats) { stats[0] = m.st.rounds; stats[1] = m.st.subrounds; stats[2] = m.st.flips; stats[3] = m.st.max_active; }
+  return 0;
+}
+
+// Warm repair after the points moved (xyz_new, input order), the way `nranks` ranks of a sharded
+// mesh do it (csrc/fishman_b200.cu repair_async): rank r sweeps the slots [T r / nranks,
+// T (r+1) / nranks) with KSweepShT into its own request list, then ALL requests are applied
+// (KApply) and the flip loop runs -- on one copy of the mesh, because every rank would do exactly
+// the same from here on.  nranks = 1 runs the unsharded dt_repair_async.  rank_order permutes the
+// order in which the ranks' requests are applied (the result must not depend on it).
+// Returns the number of turned-over triangles through *turned (> 0: the caller would rebuild).
+extern "C" int fme_repair(int n, const double* xyz_old, const double* xyz_new, int nranks, int reverse_order,
+                          int* tri_out, int* adj_out, int* turned, int* n_requests) {
+  g_err[0] = 0;
+  EmuMesh m;
+  if (m.build(n, xyz_old, 1)) return 1;
+  for (int i = 0; i < n; i++) {
+    int o = m.orig[i];
+    m.pts[i].x = xyz_new[3 * o]; m.pts[i].y = xyz_new[3 * o + 1]; m.pts[i].z = xyz_new[3 * o + 2];
   }
-  std::vector<P4> pts(n);
-  for (int i = 0; i < n; i++) pts[i] = P4{xyz[3 * orig[i]], xyz[3 * orig[i] + 1], xyz[3 * orig[i] + 2], orig[i]};
-  int T = 2 * n - 4;
-  std::vector<Row> row(T);
-  std::vector<int> loc(n, 0), rank(T + 1), flip_edge(T), role(T, 0), amark(T, 0), listA(T), listB(T), v2t(n, -1);
-  std::vector<u64> winner(T), vote(T, kNone64), mailbox(3 * (size_t)T, 0);
-  int counters[16] = {0}, err = 0;
-  std::vector<int> slow(T + 1);
-  DtCtx c;
-  memset(&c, 0, sizeof c);
-  c.n = n; c.pts = pts.data(); c.v2t = v2t.data();
-  c.row = row.data(); c.loc = loc.data(); c.winner = winner.data();
-  c.rank = rank.data(); c.vote = vote.data(); c.flip_edge = flip_edge.data(); c.role = role.data();
-  c.mailbox = mailbox.data(); c.amark = amark.data(); c.counters = counters; c.err = &err; c.slow = slow.data();
-  HostBackend be;
-  int boot[4];
-  if (dt_bootstrap(be, c, boot, g_err, sizeof g_err)) return 1;
-  for (int k = 0; k < 4; k++) loc[boot[k]] = -1;
-  DtStats st;
-  int stamp = 1;
-  int K = dt_level_count(n);
-  std::vector<int> order(n), off(K + 2, 0), prev(n);
-  std::iota(order.begin(), order.end(), 0);
-  std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
-    return point_class(pts[a].id, K) > point_class(pts[b].id, K);  // level = K - class, ascending
-  });
-  for (int i = 0; i < n; i++) off[K - point_class(pts[i].id, K) + 1]++;
-  for (int L = 0; L <= K; L++) off[L + 1] += off[L];
-  if (dt_run(be, c, listA.data(), listB.data(), order.data(), off.data(), K, prev.data(), boot, &stamp, &st,
-             g_err, sizeof g_err))
-    return 1;
-  if (c.n_tri != T) { snprintf(g_err, sizeof g_err, "triangle count %d != 2n-4", c.n_tri); return 1; }
-  for (int t = 0; t < T; t++)
-    for (int k = 0; k < 3; k++) {
-      tri_out[3 * t + k] = orig[geti(row[t].v, k)] + 1;
-      adj_out[3 * t + k] = (geti(row[t].a, k) >> 2) + 1;
+  DtCtx& c = m.c;
+  int* list[2] = {m.listA.data(), m.listB.data()};
+  *n_requests = 0;
+  if (nranks <= 1) {
+    if (dt_repair_async(m.be, c, list[0], list[1], &m.stamp, &m.st, g_err, sizeof g_err)) return 1;
+  } else {
+    int zero[15] = {0};
+    m.be.write_ints(c.counters, zero, 15);
+    c.stamp = m.stamp;
+    c.next_active = list[0];
+    c.qcount = c.counters;
+    std::vector<std::vector<int>> req(nranks);
+    std::vector<int> bnd(m.T + 1);
+    int bad = 0;
+    for (int r = 0; r < nranks; r++) {
+      int tb = (int)((long long)m.T * r / nranks), te = (int)((long long)m.T * (r + 1) / nranks);
+      req[r].assign(te - tb + 1, 0);
+      DtCtx cs = c;
+      cs.t_begin = tb; cs.req = req[r].data(); cs.bnd = bnd.data();
+      cs.blk_begin = (int)((long long)n * r / nranks); cs.blk_end = (int)((long long)n * (r + 1) / nranks);
+      c.counters[FM_C_REQ] = 0; c.counters[FM_C_BND] = 0; c.counters[3] = 0;
+      m.be.launch_filtered<KSweepShT>(cs, te - tb);
+      req[r].resize(c.counters[FM_C_REQ]);
+      bad += c.counters[3];
+      *n_requests += (int)req[r].size();
     }
-  if (stats) { stats[0] = st.rounds; stats[1] = st.subrounds; stats[2] = st.flips; stats[3] = st.max_active; }
+    c.counters[FM_C_REQ] = 0; c.counters[FM_C_BND] = 0;
+    c.counters[3] = bad;
+    for (int q = 0; q < nranks; q++) {
+      int r = reverse_order ? nranks - 1 - q : q;
+      if (reverse_order) std::reverse(req[r].begin(), req[r].end());
+      for (int msg : req[r]) KApply::run(c, msg);
+    }
+    if (bad == 0 && m.be.flip_loop(c, list, 0, true, &m.stamp, &m.st, g_err, sizeof g_err, -1)) return 1;
+  }
+  *turned = c.counters[3];
+  if (m.err) { snprintf(g_err, sizeof g_err, "error bits %d", m.err); return 1; }
+  m.export_tris(tri_out, adj_out);
   return 0;
 }

@@ -70,3 +70,24 @@ def test_emu_hemisphere_fails_cleanly():
     hemi = np.abs(points.uniform(40, 0))
     with pytest.raises(RuntimeError, match="bootstrap"):
         _emu.triangulate(hemi)
+
+
+@pytest.mark.parametrize("nranks", [2, 3, 8])
+def test_sharded_sweep_gives_the_same_mesh_as_the_unsharded_one(nranks):
+    """The N > 1 warm repair on CPU: each rank sweeps its slots into a request list, all requests
+    are applied, the flip loop runs (csrc/fishman_b200.cu repair_async, sharded).  Slot for slot
+    the result equals the unsharded repair, whatever order the requests arrive in, and it is the
+    Delaunay triangulation of the moved points."""
+    rng = np.random.default_rng(5)
+    p = points.fibonacci(3000, 2, 0.2)
+    q = p + 0.25 * np.sqrt(4 * np.pi / len(p)) * rng.normal(size=p.shape) * 0.3
+    q /= np.linalg.norm(q, axis=1)[:, None]
+    tri1, adj1, turned1, _ = _emu.repair(p, q, 1)
+    assert turned1 == 0
+    for rev in (False, True):
+        tri, adj, turned, nreq = _emu.repair(p, q, nranks, reverse=rev)
+        assert turned == 0 and nreq > 10
+        assert np.array_equal(tri, tri1) and np.array_equal(adj, adj1)
+    cold, _, _ = _emu.triangulate(q)
+    assert np.array_equal(_check.canonical(tri1), _check.canonical(cold))
+    _check.check_triangulation(q, tri1, adj1)
