@@ -82,6 +82,8 @@ struct DtCtx {
   int n;                       // points
   P4* pts;                     // internal (space-filling-curve) order
   int* v2t;                    // per vertex: SOME incident triangle (ring start), kept by split/flip
+  int* ringc;                  // per vertex: 8 cached ring triangle ids (vd_kernels.cuh, "ring cache"), or
+                               // null; a flip invalidates the records of its four vertices
   P4* cc;                      // circumcentres per triangle, maintained by sweep/flip when non-null
   Row* row;                    // per triangle slot: v = vertices (x,y,z), CCW seen from outside;
                                // a[k] = (neighbour << 2 | its edge index) across the edge
@@ -528,6 +530,10 @@ struct KFlip {
     c.row[n] = Row{I4{va, vd, vc, 0}, I4{outer[3], outer[1], enc(t, 1), 0}};
     c.v2t[vb] = t;  // b left slot n, c left slot t (a and d only gained a triangle)
     c.v2t[vc] = n;
+    if (c.ringc) {  // the rings of all four vertices changed
+      c.ringc[8 * (size_t)va] = -1; c.ringc[8 * (size_t)vb] = -1;
+      c.ringc[8 * (size_t)vc] = -1; c.ringc[8 * (size_t)vd] = -1;
+    }
     if (c.cc) {
       P3 pa = ldp(c, va), pb = ldp(c, vb), pc = ldp(c, vc), pd = ldp(c, vd);
       bool dg1, dg2;

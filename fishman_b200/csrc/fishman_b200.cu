@@ -66,6 +66,7 @@ struct fm_handle {
   // generators (internal order) and the permutation
   P4* pts = nullptr;
   int *orig = nullptr, *inv = nullptr;
+  int* ringc = nullptr;  // ring cache of the Lloyd kernel: 8 ints per vertex
   // insertion levels: points sorted by (level, internal index), level offsets (host), scratch
   int *lvl_order = nullptr, *prev = nullptr;
   int lvl_K = 0;
@@ -192,7 +193,7 @@ struct fm_handle {
   DtCtx dt_ctx() {
     DtCtx c;
     memset(&c, 0, sizeof c);
-    c.n = n; c.pts = pts; c.v2t = v2t; c.row = rows; c.loc = loc;
+    c.n = n; c.pts = pts; c.v2t = v2t; c.ringc = ringc; c.row = rows; c.loc = loc;
     c.winner = winner; c.rank = rankbuf; c.n_tri = n_tri; c.stamp = stamp; c.stamp_dev = counters + FM_C_STAMP;
     c.vote = vote; c.flip_edge = flip_edge; c.role = role; c.mailbox = mailbox; c.amark = amark;
     c.counters = counters; c.qcount = counters; c.err = err; c.slow = rankbuf;
@@ -202,7 +203,7 @@ struct fm_handle {
     VdCtx c;
     memset(&c, 0, sizeof c);
     c.n = n; c.n_tri = n_tri; c.pts = pts; c.row = rows;
-    c.cc = cc; c.cclon = cclon; c.cclat = cclat; c.v2t = v2t;
+    c.cc = cc; c.cclon = cclon; c.cclat = cclat; c.v2t = v2t; c.ringc = ringc;
     c.deg = deg; c.ring_tri = ring_tri; c.ring_nbr = ring_nbr;
     if (rho) c.rho = *rho;
     c.cell_begin = blk_begin; c.cell_end = blk_begin + blk_count;
@@ -397,6 +398,10 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
     A(dalloc(&h->bnd, (size_t)h->inbox_cap));
   }
   A(dalloc(&h->orig, n)); A(dalloc(&h->inv, n)); A(dalloc(&h->v2t, n));
+  if (!getenv("FM_NO_RING_CACHE")) {
+    A(cudaMalloc((void**)&h->ringc, 32 * (size_t)n));
+    A(cudaMemsetAsync(h->ringc, 0xff, 32 * (size_t)n, h->stream));
+  }
   A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n));
   A(dalloc(&h->rows, T));
   A(dalloc(&h->loc, n)); A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
@@ -504,7 +509,7 @@ extern "C" void fm_destroy(fm_handle* h) {
     for (void* p : mptrs)
       if (p) cudaFree(p);
   }
-  void* ptrs[] = {h->arena, h->bnd, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
+  void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
@@ -598,6 +603,7 @@ static int triangulate_cold(fm_handle* h) {
   CudaBackend be{h};
   DtCtx c = h->dt_ctx();
   c.cc = nullptr;  // circumcentres are computed once at the end, not per flip
+  c.ringc = nullptr;  // the ring cache is invalidated as a whole after the build
   int boot[4];
   if (dt_bootstrap(be, c, boot, h->errmsg, sizeof h->errmsg)) return 1;
   fm_init_loc<<<(h->n + 255) / 256, 256, 0, h->stream>>>(h->n, h->loc, boot[0], boot[1], boot[2], boot[3]);
@@ -609,6 +615,7 @@ static int triangulate_cold(fm_handle* h) {
   h->n_tri = c.n_tri;
   if (h->n_tri != 2 * h->n - 4) { h->fail("triangle count %d != 2N-4", h->n_tri); return 1; }
   if (sort_triangles(h)) return 1;
+  if (h->ringc) FM_CUDA(cudaMemsetAsync(h->ringc, 0xff, 32 * (size_t)h->n, h->stream));  // every slot was renumbered
   h->sweep_begin = 0; h->sweep_end = h->n_tri;
   if (h->size > 1) {  // the slots that go with this rank's cells (slots are sorted by smallest vertex now)
     fm_tri_range<<<1, 32, 0, h->stream>>>(h->n_tri, h->rows, h->n_pad / h->size, h->size, h->rankbuf);

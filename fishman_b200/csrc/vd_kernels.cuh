@@ -41,6 +41,7 @@ struct VdCtx {
   const Row* row;             // triangle slots (dt_kernels.cuh)
   P4* cc;                     // circumcentres per triangle (w unused)
   double *cclon, *cclat;      // optional (may be null)
+  int* ringc;                 // ring cache: 8 ints per vertex (see KCentroid), or null
   const int* v2t;             // per vertex: some incident triangle
   int* deg;                   // per ORIGINAL id: ring length, then its exclusive scan
   int *ring_tri, *ring_nbr;   // CSR payload, 1-based output ids
@@ -263,14 +264,45 @@ struct KCentroid {
   FM_HD static double compute(const VdCtx& c, int i, int* ring, int stride) {
     P4 gq = c.pts[i];
     P3 g{gq.x, gq.y, gq.z};
-    int k, t0 = ring_start(c, i, k), t = t0, d = 0, jmin = 0, tmin = t0, kmin = k;
-    do {
-      if (d < kRingCap) ring[d * stride] = t;
-      if (t < tmin) { tmin = t; jmin = d; kmin = k; }
-      t = ring_next(c, t, k);
-      d++;
-    } while (t != t0 && d < 4096);
-    if (t != t0) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
+    int k = 0, t0 = 0, t = 0, d = 0, jmin = 0, tmin = 0, kmin = 0;
+    // Ring cache.  Walking the ring is a chain of d dependent row loads; between two Lloyd
+    // iterations only the rings around flipped edges change (a few thousand of millions of
+    // cells), so the ring of a cell -- rotated to start at its lowest triangle id, padded with
+    // -1 -- is kept in one 32-byte record.  A flip invalidates the records of its four vertices
+    // (KFlip), a rebuild all of them; an invalid or long (> 8) ring is walked, and re-cached.
+    bool cached = false;
+    if (c.ringc) {
+      const I4* rec = (const I4*)(c.ringc + 8 * (size_t)i);
+      I4 r0 = rec[0], r1 = rec[1];
+      if (r0.x >= 0) {
+        cached = true;
+        ring[0] = r0.x; ring[stride] = r0.y; ring[2 * stride] = r0.z; ring[3 * stride] = r0.w;
+        ring[4 * stride] = r1.x; ring[5 * stride] = r1.y; ring[6 * stride] = r1.z; ring[7 * stride] = r1.w;
+        d = 3 + (r0.w >= 0) + (r1.x >= 0) + (r1.y >= 0) + (r1.z >= 0) + (r1.w >= 0);
+        tmin = r0.x; jmin = 0;
+      }
+    }
+    if (!cached) {
+      t0 = ring_start(c, i, k); t = t0; tmin = t0; kmin = k;
+      do {
+        if (d < kRingCap) ring[d * stride] = t;
+        if (t < tmin) { tmin = t; jmin = d; kmin = k; }
+        t = ring_next(c, t, k);
+        d++;
+      } while (t != t0 && d < 4096);
+      if (t != t0) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
+      if (c.ringc && d <= 8) {
+        int q[8];
+        for (int s = 0; s < 8; s++) {
+          int js = jmin + s;
+          if (js >= d) js -= d;
+          q[s] = s < d ? ring[js * stride] : -1;
+        }
+        I4* rec = (I4*)(c.ringc + 8 * (size_t)i);
+        rec[0] = I4{q[0], q[1], q[2], q[3]};
+        rec[1] = I4{q[4], q[5], q[6], q[7]};
+      }
+    }
     double M0 = 0.0, M1 = 0.0, M2 = 0.0;
     const double gg = g.x * g.x + g.y * g.y + g.z * g.z;
     if (UNIFORM && d <= kRingCap) {
