@@ -37,7 +37,7 @@ ALG_BYTES = {
     "flip_loop": 0,          # cooperative kernel: all flip sub-rounds of a round (latency bound, no byte model)
     "sweep": 80,             # per triangle: tri 16 + adj 16 + vertex records amortised 32*N/T = 16 + circumcentre write 32
     "circumcentre": 64,      # tri 16 + vertex records amortised 16 + write 32
-    "centroid_update": 156,  # per cell: record r/w 32+24 + v2t 4 + adj rows amortised 16*T/N = 32 + circumcentres amortised 32*T/N = 64
+    "centroid_update": 152,  # per cell: record r/w 32+24 + ring-cache record 32 + circumcentres amortised 32*T/N = 64
     "validate": 32,
 }
 
