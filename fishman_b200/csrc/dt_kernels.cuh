@@ -385,9 +385,13 @@ typedef KCheckT<true> KCheck;
 // flip_check over T + circumcentre: the three vertices are gathered once.
 template <bool EXACT, bool SHARDED>
 struct KSweepImpl {
+  FM_HD static int slot(const DtCtx& c, int item) { return SHARDED ? c.t_begin + item : item; }
   FM_HD static void run(const DtCtx& c, int item) {
-    const int t = SHARDED ? c.t_begin + item : item;
-    Row r = c.row[t];
+    const int t = slot(c, item);
+    body(c, item, t, c.row[t]);
+  }
+  // the row is passed in so that a launcher can have the rows of several items in flight at once
+  FM_HD static void body(const DtCtx& c, int item, int t, const Row& r) {
     I4 v = r.v, a = r.a;
     // stage 1: everything that depends only on the two rows -- three vertex records and the
     // three opposite-vertex ids -- is requested before anything is consumed
