@@ -124,6 +124,7 @@ struct DtCtx {
   // listed triangles to the ranks that own their vertices (launch_kernels.cuh), so that after a
   // barrier all ranks apply the same requests and run the same flip rounds.
   int t_begin;
+  int pf_dist;                 // sweep: L2 prefetch distance in triangle slots (0 = none)
   int *req, *bnd;
   int blk_begin, blk_end;      // cells of this rank
 };
@@ -388,6 +389,11 @@ struct KSweepImpl {
   FM_HD static int slot(const DtCtx& c, int item) { return SHARDED ? c.t_begin + item : item; }
   FM_HD static void run(const DtCtx& c, int item) {
     const int t = slot(c, item);
+#if defined(__CUDA_ARCH__)
+    // The row load is a cold DRAM access at the head of a chain of three dependent gathers (half
+    // of this kernel's stall samples): ask L2 for the row a later wave of blocks will start with.
+    if (c.pf_dist > 0 && t + c.pf_dist < c.n_tri) asm volatile("prefetch.global.L2 [%0];" ::"l"(c.row + t + c.pf_dist));
+#endif
     body(c, item, t, c.row[t]);
   }
   // the row is passed in so that a launcher can have the rows of several items in flight at once

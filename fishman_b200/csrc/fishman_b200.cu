@@ -197,6 +197,8 @@ struct fm_handle {
     c.winner = winner; c.rank = rankbuf; c.n_tri = n_tri; c.stamp = stamp; c.stamp_dev = counters + FM_C_STAMP;
     c.vote = vote; c.flip_edge = flip_edge; c.role = role; c.mailbox = mailbox; c.amark = amark;
     c.counters = counters; c.qcount = counters; c.err = err; c.slow = rankbuf;
+    static const int pf_waves = getenv("FM_PREFETCH_WAVES") ? atoi(getenv("FM_PREFETCH_WAVES")) : 1;
+    c.pf_dist = pf_waves * sms * 4 * 256;  // the sweep runs 4 blocks of 256 per SM: one wave ahead
     return c;
   }
   VdCtx vd_ctx(const Density* rho) {
