@@ -222,17 +222,20 @@ __global__ void __launch_bounds__(256) fm_apply_requests(DtCtx c, PeerCtx pc, co
   use_device_stamp(c);
   const PeerSync* self = pc.sync[pc.rank];
   const int gsz = gridDim.x * blockDim.x, gid = blockIdx.x * blockDim.x + threadIdx.x;
-  for (int k = 0; k < pc.size; k++) {
-    int cnt = *(volatile const int*)&self->req_count[k];
-    if (cnt > cap) { if (gid == 0) atomicOr(c.err, FM_E_OVERFLOW); cnt = cap; }
+  int cnt[8], bad = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {  // all counts requested at once: eight independent loads, not a chain
+    cnt[k] = k < pc.size ? *(volatile const int*)&self->req_count[k] : 0;
+    bad += k < pc.size ? *(volatile const int*)&self->bad[k] : 0;
+  }
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    int n = cnt[k];
+    if (n > cap) { if (gid == 0) atomicOr(c.err, FM_E_OVERFLOW); n = cap; }
     const int* box = inbox + (size_t)k * cap;
-    for (int i = gid; i < cnt; i += gsz) KApply::run(c, box[i]);
+    for (int i = gid; i < n; i += gsz) KApply::run(c, box[i]);
   }
-  if (gid == 0) {
-    int bad = 0;
-    for (int k = 0; k < pc.size; k++) bad += *(volatile const int*)&self->bad[k];
-    c.counters[3] = bad;
-  }
+  if (gid == 0) c.counters[3] = bad;
 }
 
 // out[r] = first triangle slot whose smallest vertex is >= r * per, r = 0 .. size (slots are
