@@ -5,6 +5,8 @@
 //   Backend::launch<K>(ctx, n)            run body K for thread ids [0, n)
 //   Backend::launch_filtered<K>(ctx, n)   K<false> (fp64 filters only) for [0, n), then K<true>
 //                                         (exact) for the items K<false> deferred
+//   Backend::locate_round(ctx, m)         point location + votes of the m points of the level
+//                                         (= launch_filtered<KLocateVoteT>, or its sharded form)
 //   Backend::fill64(ptr, value, count)    device memset of 64-bit words
 //   Backend::fill32(ptr, value, count)
 //   Backend::exclusive_scan(ptr, n)       in place over ints; returns the total
@@ -234,7 +236,7 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
     while (remaining > 0) {
       st->rounds++;
       be.fill64(c.winner, kNone64, (size_t)c.n_tri);
-      be.template launch_filtered<KLocateVoteT>(c, m);
+      be.locate_round(c, m);
       be.template launch<KSplitFlag>(c, c.n_tri);
       int nsplit = be.exclusive_scan(c.rank, c.n_tri);
       be.read_ints(host, c.err, 1);

@@ -92,6 +92,7 @@ struct DtCtx {
   const int* plist;            // points taking part in this round (the current insertion level), or
                                // null = all points; thread i of the locate kernels handles plist[i]
   int n_plist;
+  int locate_only;             // sharded point location: walk and record loc[], the votes are cast later (KVote)
   const int* prev;             // per point: nearest point to the left (internal order) of a coarser level
   int level_thr;               // coarseness of the current level
   int level_max;               // coarsest class K
@@ -287,11 +288,24 @@ struct KLocateVoteT {
     FM_ATOMIC_ADD32(&c.counters[13], 1);
     if (steps > 30) FM_ATOMIC_ADD32(&c.counters[14], 1);
 #endif
+    if (c.locate_only) return;
     u64 key = ((u64)hash32((unsigned)qi) << 32) | (unsigned)p;
     FM_ATOMIC_MIN64(&c.winner[t], key);
   }
 };
 typedef KLocateVoteT<true> KLocateVote;
+
+// Sharded point location, second half (every rank, over ALL points of the level): the vote of a
+// point for the triangle its walk ended in -- on whichever rank that walk ran.
+struct KVote {
+  FM_HD static void run(const DtCtx& c, int i) {
+    int p = c.plist ? c.plist[i] : i;
+    int t = c.loc[p];
+    if (t < 0) return;
+    u64 key = ((u64)hash32((unsigned)c.pts[p].id) << 32) | (unsigned)p;
+    FM_ATOMIC_MIN64(&c.winner[t], key);
+  }
+};
 
 // One thread per triangle: 1 if it splits this round (input of the scan).
 struct KSplitFlag {

@@ -31,6 +31,7 @@ template <class K> struct KName { static const char* get() { return "kernel"; } 
 FM_KNAME(KLocateVote, "locate_exact")
 FM_KNAME(KLocateVoteT<false>, "locate_vote")
 FM_KNAME(KSplitFlag, "split_flag")
+FM_KNAME(KVote, "vote")
 FM_KNAME(KLevelInit, "level_init")
 FM_KNAME(KSplit, "split13")
 FM_KNAME(KCheck, "check_exact")
@@ -104,7 +105,8 @@ struct fm_handle {
   int* inbox = nullptr;       // size regions of inbox_cap flip requests, one per sending rank
   int* bnd = nullptr;         // swept triangles with a vertex on another rank (inbox_cap entries)
   int inbox_cap = 0;
-  size_t off_sync = 0, off_inbox = 0, off_cc = 0;  // arena layout (the same on every rank)
+  size_t off_sync = 0, off_inbox = 0, off_cc = 0, off_loc = 0;  // arena layout (the same on every rank)
+  bool shard_locate = true;   // peers attached: split each level's point location over the ranks
   int sweep_begin = 0, sweep_end = 0;              // triangle slots this rank sweeps (sharded warm repair)
   void* peer_base[8] = {nullptr};
   PeerCtx peer_ctx = {};
@@ -231,6 +233,11 @@ struct CudaBackend {
     h->note_cuda(cudaGetLastError(), KName<K<true>>::get());
     h->prof_end(KName<K<true>>::get(), 0);
   }
+  // Point location of one level.  On a sharded mesh with attached peers: this rank walks its slice
+  // of the level's points (no votes), its results go to every rank's loc[] over NVLink, barrier,
+  // then every rank casts all votes -- the triangulation stays replicated and identical.  Small
+  // levels are not worth the exchange and are located whole on every rank.
+  void locate_round(DtCtx& c, int m);
   void fill64(u64* p, u64 v, size_t n) {
     // only all-ones is ever requested: a byte memset does it
     h->note_cuda(cudaMemsetAsync(p, (int)(v & 0xff), n * sizeof(u64), h->stream), "fill64");
@@ -339,6 +346,31 @@ struct CudaBackend {
   }
 };
 
+static void launch_peer_barrier(fm_handle* h, int phase);
+void CudaBackend::locate_round(DtCtx& c, int m) {
+  const int kMinPerRank = 16384;
+  if (!(h->peers_attached && h->shard_locate) || m < kMinPerRank * h->size) {
+    launch_filtered<KLocateVoteT>(c, m);
+    return;
+  }
+  int mb = (int)((long long)m * h->rank / h->size), me = (int)((long long)m * (h->rank + 1) / h->size);
+  DtCtx cs = c;
+  cs.plist = c.plist + mb;
+  cs.locate_only = 1;
+  launch_filtered<KLocateVoteT>(cs, me - mb);
+  LocFan f = {};
+  for (int k = 0; k < h->size; k++)
+    f.loc[k] = (int*)(((k == h->rank) ? h->arena : (char*)h->peer_base[k]) + h->off_loc);
+  f.plist = cs.plist; f.rank = h->rank; f.size = h->size;
+  launch_peer_barrier(h, 3);  // every rank is done with the previous round's votes and splits: loc[] may be overwritten
+  h->prof_begin();
+  fm_loc_fanout<<<(me - mb + 255) / 256, 256, 0, h->stream>>>(f, me - mb);
+  h->note_cuda(cudaGetLastError(), "loc_fanout");
+  h->prof_end("loc_fanout", me - mb);
+  launch_peer_barrier(h, 3);
+  launch<KVote>(c, m);
+}
+
 // ---------------------------------------------------------------------- API
 template <class T>
 static cudaError_t dalloc(T** p, size_t count) {
@@ -391,7 +423,10 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
     h->off_sync = up(sizeof(P4) * (size_t)h->n_pad);
     h->off_inbox = up(h->off_sync + sizeof(PeerSync));
     h->off_cc = up(h->off_inbox + sizeof(int) * (size_t)h->inbox_cap * size);
-    A(cudaMalloc((void**)&h->arena, h->off_cc + sizeof(P4) * T));
+    h->off_loc = up(h->off_cc + sizeof(P4) * T);
+    A(cudaMalloc((void**)&h->arena, h->off_loc + sizeof(int) * (size_t)n));
+    h->loc = (int*)(h->arena + h->off_loc);
+    if (const char* e = getenv("FM_SHARD_LOCATE")) h->shard_locate = atoi(e) != 0;
     h->pts = (P4*)h->arena;
     h->psync = (PeerSync*)(h->arena + h->off_sync);
     h->inbox = (int*)(h->arena + h->off_inbox);
@@ -406,7 +441,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   }
   A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n));
   A(dalloc(&h->rows, T));
-  A(dalloc(&h->loc, n)); A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
+  A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T));
   A(dalloc(&h->counters, 16));
   h->err = h->counters + FM_C_ERR;
@@ -511,7 +546,7 @@ extern "C" void fm_destroy(fm_handle* h) {
     for (void* p : mptrs)
       if (p) cudaFree(p);
   }
-  void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->loc, h->rankbuf, h->flip_edge,
+  void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};

@@ -148,7 +148,8 @@ struct PeerCtx {
 // phase 0 (before the centroid kernel: every rank has finished reading the generators),
 // phase 1 (after it: every rank's stores into this rank's generator array have landed, and the
 // displacement maxima have been combined) and phase 2 (after a sharded sweep: every rank's flip
-// requests and circumcentres have landed here, and their counts are known).  One warp; lane k talks to rank k.  A rank that does
+// requests and circumcentres have landed here, and their counts are known); phase 3 is a plain
+// barrier (sharded point location).  One warp; lane k talks to rank k.  A rank that does
 // not show up within ~2 s of SM clocks sets FM_E_PEER instead of hanging the device.
 __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
   __shared__ int ep;
@@ -182,6 +183,20 @@ __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
     __threadfence_system();
     *(volatile u64*)(counters + FM_C_MAXDISP) = *(volatile u64*)&self->maxdisp_all;
   }
+}
+
+// Sharded point location: the slots this rank's walks ended in, to every rank's loc[]
+struct LocFan {
+  int* loc[8];      // by rank
+  const int* plist; // this rank's slice of the level
+  int rank, size;
+};
+__global__ void __launch_bounds__(256) fm_loc_fanout(LocFan f, int m) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  int p = f.plist[i], v = f.loc[f.rank][p];
+  for (int k = 0; k < f.size; k++)
+    if (k != f.rank) f.loc[k][p] = v;
 }
 
 // Fan-out of a sharded sweep's findings over NVLink: the flip requests to every rank's inbox

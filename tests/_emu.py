@@ -65,3 +65,18 @@ def repair(xyz_old, xyz_new, nranks=1, reverse=False):
     if rc:
         raise RuntimeError(lib().fme_last_error().decode())
     return tri, adj, turned.value, nreq.value
+
+
+def triangulate_sharded(xyz, nranks):
+    """Cold build with every level's point location done in nranks slices (the sharded form)."""
+    p = np.ascontiguousarray(xyz, dtype=np.float64)
+    n = len(p)
+    T = 2 * n - 4
+    tri = np.empty((T, 3), np.int32)
+    adj = np.empty((T, 3), np.int32)
+    ip = C.POINTER(C.c_int)
+    rc = lib().fme_triangulate_sharded(n, p.ctypes.data_as(C.POINTER(C.c_double)), int(nranks),
+                                       tri.ctypes.data_as(ip), adj.ctypes.data_as(ip))
+    if rc:
+        raise RuntimeError(lib().fme_last_error().decode())
+    return tri, adj

@@ -28,6 +28,21 @@ struct HostBackend {
     c.counters[FM_C_SLOW] = 0;
   }
   long long n_deferred = 0;
+  // point location of a level: whole, or (shard_ranks > 1) the way the ranks of a sharded mesh
+  // do it -- each rank walks its slice of the level recording loc[] only, then all votes are cast
+  int shard_ranks = 1;
+  void locate_round(DtCtx& c, int m) {
+    if (shard_ranks <= 1) { launch_filtered<KLocateVoteT>(c, m); return; }
+    const int* plist = c.plist;
+    for (int r = 0; r < shard_ranks; r++) {
+      int mb = (int)((long long)m * r / shard_ranks), me = (int)((long long)m * (r + 1) / shard_ranks);
+      DtCtx cs = c;
+      cs.plist = plist + mb;
+      cs.locate_only = 1;
+      launch_filtered<KLocateVoteT>(cs, me - mb);
+    }
+    launch<KVote>(c, m);
+  }
   void fill64(u64* p, u64 v, size_t n) { std::fill(p, p + n, v); }
   void fill32(int* p, int v, size_t n) { std::fill(p, p + n, v); }
   int exclusive_scan(int* p, int n) {
@@ -139,6 +154,16 @@ extern "C" int fme_triangulate(int n, const double* xyz, int* tri_out, int* adj_
   if (m.build(n, xyz, do_sort)) return 1;
   m.export_tris(tri_out, adj_out);
   if (stats) { stats[0] = m.st.rounds; stats[1] = m.st.subrounds; stats[2] = m.st.flips; stats[3] = m.st.max_active; }
+  return 0;
+}
+
+// cold build with the point location of every level done in `nranks` slices (sharded form)
+extern "C" int fme_triangulate_sharded(int n, const double* xyz, int nranks, int* tri_out, int* adj_out) {
+  g_err[0] = 0;
+  EmuMesh m;
+  m.be.shard_ranks = nranks;
+  if (m.build(n, xyz, 1)) return 1;
+  m.export_tris(tri_out, adj_out);
   return 0;
 }
 

@@ -91,3 +91,13 @@ def test_sharded_sweep_gives_the_same_mesh_as_the_unsharded_one(nranks):
     cold, _, _ = _emu.triangulate(q)
     assert np.array_equal(_check.canonical(tri1), _check.canonical(cold))
     _check.check_triangulation(q, tri1, adj1)
+
+
+@pytest.mark.parametrize("nranks", [2, 5])
+def test_sharded_point_location_gives_the_same_build(nranks):
+    """Cold build with each level's point location split over ranks (walks record loc[] only, the
+    votes are cast afterwards from all ranks' results): slot for slot the unsharded build."""
+    p = points.uniform(3000, 7)
+    tri1, adj1, _ = _emu.triangulate(p)
+    tri, adj = _emu.triangulate_sharded(p, nranks)
+    assert np.array_equal(tri, tri1) and np.array_equal(adj, adj1)

@@ -39,6 +39,25 @@ def main():
 
     a = fb.Mesh.from_xyz(p, rank=rank, size=world)
     a.peer_connect(dist)
+    # the cold build on the sharded mesh (point location split over the ranks) against the single-GPU one
+    a.delaunay_triangulation()
+    tri_cold = a.triangles()[0]
+    ref2 = fb.Mesh.from_xyz(p)
+    ref2.delaunay_triangulation()
+    cold_equal = np.array_equal(tri_cold, ref2.triangles()[0])
+    prof = None
+    if os.environ.get("FM_CHECK_TIME"):
+        import time
+        ts = []
+        for mesh in (a, ref2):
+            dist.barrier(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                mesh.delaunay_triangulation()
+            torch.cuda.synchronize()
+            ts.append((time.perf_counter() - t0) / 3 * 1e3)
+        prof = f"cold build ms: sharded {ts[0]:.2f} single {ts[1]:.2f}"
+    ref2.close()
     md_a = [a.lloyd(rho, max_iter=1, warm=True)[1] for _ in range(iters)]
     g_a = a.generators()
     st_a = a.stats()
@@ -57,7 +76,8 @@ def main():
     g_b = b.generators()
     b.close()
 
-    ok = (np.array_equal(g_ref, g_a) and np.array_equal(g_ref, g_b) and md_ref == md_a and md_ref == md_b)
+    print(f"rank {rank}: sharded cold build == single, slot for slot: {cold_equal}" + (f"; {prof}" if prof else ""), flush=True)
+    ok = cold_equal and (np.array_equal(g_ref, g_a) and np.array_equal(g_ref, g_b) and md_ref == md_a and md_ref == md_b)
     print(f"rank {rank}/{world}: n={n} iters={iters} p2p==single {np.array_equal(g_ref, g_a)} "
           f"nccl==single {np.array_equal(g_ref, g_b)} maxdisp equal {md_ref == md_a and md_ref == md_b} "
           f"last maxdisp {md_ref[-1]:.3e}", flush=True)
