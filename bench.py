@@ -185,7 +185,7 @@ def run_reference(args):
 def workload_config(args):
     return {"workload": f"C4: {args.n}-generator uniform-density SCVT Lloyd loop (BASELINE.json configs[3]); "
                         "FIB lattice + 0.2h jitter, seed 0",
-            "mode": args.mode, "density": "uniform", "generators": args.n,
+            "mode": args.mode, "density": args.density, "generators": args.n,
             "parallelism": (f"replicated DT + sharded centroid x{args.gpus}, generator exchange: "
                             + ("stores into peer memory over NVLink from the Lloyd kernel" if args.exchange == "p2p"
                                else "NCCL all-gather")) if args.gpus > 1 else "single GPU",
@@ -213,7 +213,7 @@ def run_gpu(args):
     n = args.n
     p = make_points(n)
     warm = args.mode == "warm"
-    rho = fb.density_uniform()
+    rho = fb.density_uniform() if args.density == "uniform" else fb.density_x4()
     m = fb.Mesh.from_xyz(p, rank=rank, size=world)
     gather = None
     if world > 1 and args.exchange == "p2p" and torch.cuda.device_count() < world:
@@ -350,6 +350,8 @@ def main():
     ap.add_argument("--mode", default="warm", choices=["warm", "cold"])
     ap.add_argument("--n", type=int, default=N_C4)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--density", default="uniform", choices=["uniform", "x4"],
+                    help="x4: the 4:1 regional refinement density of configs[2] (not the headline workload)")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how the updated generator blocks reach the other ranks")
     args = ap.parse_args()
