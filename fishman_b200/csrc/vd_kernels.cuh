@@ -135,7 +135,13 @@ FM_HD inline double density_eval(const Density& r, double x, double y, double z)
   if (r.kind == 0) return 1.0;
   double dot = x * r.cx + y * r.cy + z * r.cz;
   double d = acos(fmax(fmin(dot, 1.0), -1.0));  // calc_arc_length, sphere_geometry_mod.F90:289-296
+#if defined(__CUDA_ARCH__)
+  // (tanh(u) + 1) / 2 = 1 / (1 + exp(-2u)): one exp and one division instead of the library tanh
+  // (itself an exp, a division and range branches); the same value to a few ulp
+  return (1.0 - r.gamma) / (1.0 + exp(-2.0 * ((r.beta - d) / r.alpha))) + r.gamma;
+#else
   return 0.5 * (1.0 - r.gamma) * (tanh((r.beta - d) / r.alpha) + 1.0) + r.gamma;
+#endif
 }
 
 // degree-5 seven-point rule on a triangle (barycentric weights of g, c_j, c_j+1)
