@@ -85,6 +85,39 @@ def test_c3_655362_variable_density():
     m.close()
 
 
+def test_c5_ten_million_uniform_random_points():
+    """configs[4]: one-shot Delaunay triangulation of 10M uniform random points.  Structure
+    (counts, Euler, adjacency symmetry, orientation), idempotence of the repair, the local
+    Delaunay property on every edge, and rebuild determinism."""
+    import fishman_b200 as fb
+    from fishman_b200 import points
+    n = 10_000_000
+    p = points.uniform(n, 0)
+    m = fb.Mesh.from_xyz(p)
+    m.delaunay_triangulation()
+    tri, adj = m.triangles()
+    assert tri.shape == (2 * n - 4, 3)
+    _check.check_triangulation(p, tri, adj)
+    m.stats_reset()
+    m.retriangulate(warm=True)
+    assert m.stats()["flips"] == 0
+    t0 = tri.astype(np.int64) - 1
+    a0 = adj.astype(np.int64) - 1
+    worst = 0.0
+    for k in range(3):
+        nb = t0[a0[:, k]]
+        mask = (nb != t0[:, [(k + 1) % 3]]) & (nb != t0[:, [(k + 2) % 3]])
+        d = p[nb[mask]]
+        det = np.einsum("ij,ij->i", p[t0[:, 2]] - d, np.cross(p[t0[:, 1]] - d, p[t0[:, 0]] - d))
+        worst = max(worst, float(det.max()))
+        del nb, mask, d, det
+    assert worst <= 2.220446049250313e-16, worst   # DV:2051-2061 with the reference's eps
+    m.retriangulate(warm=False)
+    tri2, _ = m.triangles()
+    assert np.array_equal(tri, tri2)
+    m.close()
+
+
 def test_multi_gpu_bit_identical():
     """2 ranks, one per GPU: peer-exchange path and NCCL path against one GPU (tools/dist_check.py)."""
     import torch
