@@ -990,6 +990,8 @@ static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool gua
   d.kind = rho ? rho->kind : 0;
   if (rho) { d.cx = rho->cx; d.cy = rho->cy; d.cz = rho->cz; d.beta = rho->beta; d.alpha = rho->alpha; d.gamma = rho->gamma; }
   else { d.cx = d.cy = 0; d.cz = 1; d.beta = 0; d.alpha = 1; d.gamma = 1; }
+  d.k2 = 2.0 / d.alpha;
+  d.c2 = -d.beta * d.k2;
   VdCtx c = h->vd_ctx(&d);
   c.abort_flag = guarded ? h->counters + 3 : nullptr;
   int cnt = h->blk_count;

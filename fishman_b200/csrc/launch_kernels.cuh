@@ -107,8 +107,11 @@ __global__ void fm_subround_end(int* counters, int cur, int nact) {
 #ifndef FM_OCC_CENTROID
 #define FM_OCC_CENTROID 8
 #endif
+#ifndef FM_OCC_CENTROID_RHO
+#define FM_OCC_CENTROID_RHO 4   // with a density: seven evaluations in flight per sub-triangle want ~128 registers
+#endif
 template <bool UNIFORM>
-__global__ void __launch_bounds__(128, FM_OCC_CENTROID) fm_centroid_update(const VdCtx c, int n) {
+__global__ void __launch_bounds__(128, UNIFORM ? FM_OCC_CENTROID : FM_OCC_CENTROID_RHO) fm_centroid_update(const VdCtx c, int n) {
   extern __shared__ int ring_smem[];
   if (c.abort_flag && *c.abort_flag) return;
   int j = blockIdx.x * blockDim.x + threadIdx.x;

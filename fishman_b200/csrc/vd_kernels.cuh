@@ -30,9 +30,10 @@ FM_HD inline u64 dbits(double v) {
 #endif
 }
 
-struct Density {   // same layout as fm_density in include/fishman_b200.h
+struct Density {   // the first seven members: same layout as fm_density in include/fishman_b200.h
   int kind;        // 0 uniform, 1 tanh refinement
   double cx, cy, cz, beta, alpha, gamma;
+  double k2, c2;   // 2/alpha and -2 beta/alpha, set by the launcher: -2 (beta - d)/alpha = d k2 + c2
 };
 
 struct VdCtx {
@@ -135,12 +136,83 @@ FM_HD inline double density_eval(const Density& r, double x, double y, double z)
   if (r.kind == 0) return 1.0;
   double dot = x * r.cx + y * r.cy + z * r.cz;
   double d = acos(fmax(fmin(dot, 1.0), -1.0));  // calc_arc_length, sphere_geometry_mod.F90:289-296
-#if defined(__CUDA_ARCH__)
-  // (tanh(u) + 1) / 2 = 1 / (1 + exp(-2u)): one exp and one division instead of the library tanh
-  // (itself an exp, a division and range branches); the same value to a few ulp
-  return (1.0 - r.gamma) / (1.0 + exp(-2.0 * ((r.beta - d) / r.alpha))) + r.gamma;
-#else
   return 0.5 * (1.0 - r.gamma) * (tanh((r.beta - d) / r.alpha) + 1.0) + r.gamma;
+}
+
+#if defined(__CUDACC__)
+// ---- the same density on the device, 42 evaluations per cell.  The library acos / exp / IEEE
+// divisions came to ~195 issued instructions per evaluation, a third of them moves of 64-bit
+// immediates (two UMOV per polynomial coefficient) and NaN-exact fmin/fmax sequences.  Here: the
+// coefficients sit in constant memory (an operand of the DFMA itself), no range branches, no
+// library calls.
+//   rho = (1 - gamma) / (1 + exp(-2 (beta - d)/alpha)) + gamma     ((tanh u + 1)/2 = 1/(1 + e^-2u))
+// fm_acos: |x| <= 1/2: pi/2 - asin x;  |x| > 1/2: 2 asin sqrt((1 - |x|)/2), pi - that for x < 0;
+//   asin s = s + s z P(z), z = s^2, P = degree-12 fit of (asin(sqrt z)/sqrt z - 1)/z on [0, 1/4]
+//   (Chebyshev nodes, 50-digit arithmetic, |z P - exact| < 6e-18).  |x| a rounding above 1 gives
+//   z < 0 -> s = 0 -> 0 or pi: no clamp needed.  Measured on the device against libm over
+//   [-1, 1] incl. 1 - 1e-16: absolute error <= 4.5e-16, relative <= 3.6e-16.
+// fm_exp: t in [-700, 700]: n = rint(t log2 e), r = t - n ln2 (two FMAs, ln2 split hi/lo),
+//   e^r = 1 + r + r^2 Q(r), Q = degree-10 fit on |r| <= ln2/2 (relative error 4e-19), 2^n by an
+//   integer add into the exponent field (the result is normal on that range).
+static __constant__ double kAsinP[13] = {
+    0.16666666666666669, 0.07499999999998433, 0.04464285714635543, 0.030381944138531247,
+    0.02237217294214989, 0.017352392720869973, 0.013971212973552933, 0.011479177415184906,
+    0.01032281435018578, 0.005457506718640358, 0.01740087944269402, -0.014851887071247204,
+    0.028757851367421566};
+static __constant__ double kExpQ[11] = {
+    0.5, 0.1666666666666667, 0.04166666666666667, 0.008333333333326136, 0.0013888888888883748,
+    0.00019841269874820627, 2.4801587325547743e-05, 2.7557255400206422e-06, 2.75572736431103e-07,
+    2.5105217004720745e-08, 2.0914686968086876e-09};
+
+// 1/v for v > 0: hardware seed (MUFU.RCP64H, ~2^-20) + one cubic step y (1 + e + e^2), e = 1 - v y
+__device__ __forceinline__ double fm_rcp(double v) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
+  double e = fma(-v, y, 1.0);
+  return fma(y, fma(e, e, e), y);
+}
+__device__ __forceinline__ double fm_acos(double x) {
+  const double a = fabs(x);
+  const bool lo = a <= 0.5;
+  const double z = lo ? x * x : 0.5 * (1.0 - a);   // 1 - a is exact for a >= 1/2
+  double r;                                         // 1/sqrt(z): seed + one cubic step, as fm_rsqrt
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(z));
+  const double e = fma(-(z * r), r, 1.0);
+  r = fma(r, fma(0.375, e, 0.5) * e, r);
+  const double s = lo ? a : (z > 0.0 ? z * r : 0.0);
+  double p = kAsinP[12];
+#pragma unroll
+  for (int k = 11; k >= 0; k--) p = fma(p, z, kAsinP[k]);
+  const double t = fma(s, z * p, s);   // asin s
+  const double pio2_hi = 1.5707963267948966, pio2_lo = 6.123233995736766e-17;
+  const double u = (lo && x < 0.0) ? -t : t;                  // lo: asin x;  otherwise asin s
+  const double v = pio2_hi - (u - pio2_lo);                   // lo: acos x;  x < -1/2: (acos x)/2
+  return lo ? v : (x > 0.0 ? 2.0 * t : 2.0 * v);
+}
+__device__ __forceinline__ double fm_exp(double t) {  // t in [-700, 700]
+  const double magic = 6755399441055744.0;            // 1.5 * 2^52: the low word of t' + magic is rint(t')
+  const double nm = fma(t, 1.4426950408889634, magic);
+  const double n = nm - magic;
+  double r = fma(n, -0.6931471805599453, t);
+  r = fma(n, -2.3190468138462996e-17, r);
+  double q = kExpQ[10];
+#pragma unroll
+  for (int k = 9; k >= 0; k--) q = fma(q, r, kExpQ[k]);
+  const double p = fma(r * r, q, r) + 1.0;
+  return __hiloint2double(__double2hiint(p) + (__double2loint(nm) << 20), __double2loint(p));
+}
+#endif
+// density at the projected node q/|q|, given q and inv = 1/|q|
+FM_HD inline double density_node(const Density& r, double qx, double qy, double qz, double inv) {
+#if defined(__CUDA_ARCH__)
+  const double dot = fma(qz, r.cz, fma(qy, r.cy, qx * r.cx)) * inv;
+  const double d = fm_acos(dot);
+  double t = fma(d, r.k2, r.c2);   // -2 (beta - d)/alpha
+  t = t > 700.0 ? 700.0 : t;
+  t = t < -700.0 ? -700.0 : t;
+  return fma(1.0 - r.gamma, fm_rcp(1.0 + fm_exp(t)), r.gamma);
+#else
+  return density_eval(r, qx * inv, qy * inv, qz * inv);
 #endif
 }
 
@@ -199,13 +271,13 @@ FM_HD inline void quad_subtriangle(const Density& r, const P3& g, const P3& a, c
   double w1g = FM_QW1 * i1g, w1a = FM_QW1 * i1a, w1b = FM_QW1 * i1b;
   double w2g = FM_QW2 * i2g, w2a = FM_QW2 * i2a, w2b = FM_QW2 * i2b;
   if (!UNIFORM) {  // density at the projected nodes q^ = (S + kappa v) / |q|
-    w0 *= density_eval(r, S0 * i0, S1 * i0, S2 * i0);
-    w1g *= density_eval(r, fma(k1, g.x, S0) * i1g, fma(k1, g.y, S1) * i1g, fma(k1, g.z, S2) * i1g);
-    w1a *= density_eval(r, fma(k1, a.x, S0) * i1a, fma(k1, a.y, S1) * i1a, fma(k1, a.z, S2) * i1a);
-    w1b *= density_eval(r, fma(k1, b.x, S0) * i1b, fma(k1, b.y, S1) * i1b, fma(k1, b.z, S2) * i1b);
-    w2g *= density_eval(r, fma(k2, g.x, S0) * i2g, fma(k2, g.y, S1) * i2g, fma(k2, g.z, S2) * i2g);
-    w2a *= density_eval(r, fma(k2, a.x, S0) * i2a, fma(k2, a.y, S1) * i2a, fma(k2, a.z, S2) * i2a);
-    w2b *= density_eval(r, fma(k2, b.x, S0) * i2b, fma(k2, b.y, S1) * i2b, fma(k2, b.z, S2) * i2b);
+    w0 *= density_node(r, S0, S1, S2, i0);
+    w1g *= density_node(r, fma(k1, g.x, S0), fma(k1, g.y, S1), fma(k1, g.z, S2), i1g);
+    w1a *= density_node(r, fma(k1, a.x, S0), fma(k1, a.y, S1), fma(k1, a.z, S2), i1a);
+    w1b *= density_node(r, fma(k1, b.x, S0), fma(k1, b.y, S1), fma(k1, b.z, S2), i1b);
+    w2g *= density_node(r, fma(k2, g.x, S0), fma(k2, g.y, S1), fma(k2, g.z, S2), i2g);
+    w2a *= density_node(r, fma(k2, a.x, S0), fma(k2, a.y, S1), fma(k2, a.z, S2), i2a);
+    w2b *= density_node(r, fma(k2, b.x, S0), fma(k2, b.y, S1), fma(k2, b.z, S2), i2b);
   }
   double cS = w0 + ((w1g + w1a) + w1b) + ((w2g + w2a) + w2b);
   double cg = fma(k1, w1g, k2 * w2g), ca = fma(k1, w1a, k2 * w2a), cb = fma(k1, w1b, k2 * w2b);
