@@ -243,15 +243,22 @@ __global__ void __launch_bounds__(256) fm_apply_requests(DtCtx c, PeerCtx pc, co
   int cnt[8], bad = 0;
 #pragma unroll
   for (int k = 0; k < 8; k++) {  // all counts requested at once: eight independent loads, not a chain
-    cnt[k] = k < pc.size ? *(volatile const int*)&self->req_count[k] : 0;
+    int n = k < pc.size ? *(volatile const int*)&self->req_count[k] : 0;
     bad += k < pc.size ? *(volatile const int*)&self->bad[k] : 0;
-  }
-#pragma unroll
-  for (int k = 0; k < 8; k++) {
-    int n = cnt[k];
     if (n > cap) { if (gid == 0) atomicOr(c.err, FM_E_OVERFLOW); n = cap; }
-    const int* box = inbox + (size_t)k * cap;
-    for (int i = gid; i < n; i += gsz) KApply::run(c, box[i]);
+    cnt[k] = n;
+  }
+  // ONE index space over the requests of all ranks (a loop per sending rank would run `size`
+  // latency chains -- request, row, two atomics -- one after the other)
+  int total = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) total += cnt[k];
+  for (int i = gid; i < total; i += gsz) {
+    int j = i, k = 0;
+#pragma unroll
+    for (int q = 0; q < 7; q++)
+      if (k == q && j >= cnt[q]) { j -= cnt[q]; k = q + 1; }
+    KApply::run(c, inbox[(size_t)k * cap + j]);
   }
   if (gid == 0) c.counters[3] = bad;
 }
