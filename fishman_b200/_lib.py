@@ -12,7 +12,7 @@ SYMBOLS = [
     "fm_create", "fm_create_lonlat", "fm_create_dist", "fm_destroy", "fm_last_error", "fm_triangulate", "fm_retriangulate",
     "fm_counts", "fm_get_triangles", "fm_voronoi", "fm_get_circumcentres", "fm_get_rings",
     "fm_get_edges", "fm_mpas", "fm_get_mpas_edges", "fm_get_mpas_cells", "fm_get_mpas_vertices",
-    "fm_get_mpas_edges_on_edge", "fm_lloyd", "fm_lloyd_local", "fm_generator_block", "fm_peer_handle", "fm_peer_attach", "fm_get_generators",
+    "fm_get_mpas_edges_on_edge", "fm_lloyd", "fm_lloyd_local", "fm_generator_block", "fm_peer_handle", "fm_peer_attach", "fm_density_eval", "fm_get_generators",
     "fm_set_generators", "fm_host_alloc", "fm_host_free", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
     "fm_profile_enable", "fm_profile_get", "fm_device_info",
 ]
@@ -59,6 +59,7 @@ def lib():
     L.fm_generator_block.argtypes = [vp, C.POINTER(vp), i64p, i64p, i64p]
     L.fm_peer_handle.argtypes = [vp, C.c_char_p]
     L.fm_peer_attach.argtypes = [vp, C.c_char_p]
+    L.fm_density_eval.argtypes = [C.POINTER(Density), C.c_int64, dp, dp, dp, dp]
     L.fm_get_generators.argtypes = [vp, dp, dp, dp]
     L.fm_set_generators.argtypes = [vp, dp, dp, dp]
     L.fm_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]

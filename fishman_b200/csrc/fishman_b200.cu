@@ -975,6 +975,7 @@ static void launch_peer_barrier(fm_handle* h, int phase) {
   h->prof_end("peer_barrier", 0);
 }
 
+static Density make_density(const fm_density* rho);
 static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded);
 // Centroid stage of one iteration.  On a sharded mesh with attached peers the kernel runs
 // between two barriers: no rank overwrites generators another rank is still reading, and the
@@ -986,12 +987,7 @@ static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded) {
 }
 
 static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded) {
-  Density d;
-  d.kind = rho ? rho->kind : 0;
-  if (rho) { d.cx = rho->cx; d.cy = rho->cy; d.cz = rho->cz; d.beta = rho->beta; d.alpha = rho->alpha; d.gamma = rho->gamma; }
-  else { d.cx = d.cy = 0; d.cz = 1; d.beta = 0; d.alpha = 1; d.gamma = 1; }
-  d.k2 = 2.0 / d.alpha;
-  d.c2 = -d.beta * d.k2;
+  Density d = make_density(rho);
   VdCtx c = h->vd_ctx(&d);
   c.abort_flag = guarded ? h->counters + 3 : nullptr;
   int cnt = h->blk_count;
@@ -1196,6 +1192,41 @@ extern "C" int fm_get_generators(fm_handle* h, double* x, double* y, double* z) 
 }
 extern "C" int fm_set_generators(fm_handle* h, const double* x, const double* y, const double* z) {
   return xfer_generators(h, (double*)x, (double*)y, (double*)z, false);
+}
+
+static Density make_density(const fm_density* rho) {
+  Density d;
+  d.kind = rho ? rho->kind : 0;
+  if (rho) { d.cx = rho->cx; d.cy = rho->cy; d.cz = rho->cz; d.beta = rho->beta; d.alpha = rho->alpha; d.gamma = rho->gamma; }
+  else { d.cx = d.cy = 0; d.cz = 1; d.beta = 0; d.alpha = 1; d.gamma = 1; }
+  d.k2 = 2.0 / d.alpha;
+  d.c2 = -d.beta * d.k2;
+  return d;
+}
+
+__global__ void fm_density_points(Density d, long long n, const double* x, const double* y, const double* z, double* out) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = density_node(d, x[i], y[i], z[i], 1.0);
+}
+extern "C" int fm_density_eval(const fm_density* rho, int64_t n, const double* x, const double* y, const double* z,
+                               double* out) {
+  if (n <= 0) return 0;
+  double* dev = nullptr;
+  size_t bytes = sizeof(double) * (size_t)n;
+  if (cudaMalloc((void**)&dev, 4 * bytes) != cudaSuccess) {
+    snprintf(g_create_err, sizeof g_create_err, "fm_density_eval: no CUDA device or out of memory");
+    return 1;
+  }
+  bool ok = cudaMemcpy(dev, x, bytes, cudaMemcpyHostToDevice) == cudaSuccess &&
+            cudaMemcpy(dev + n, y, bytes, cudaMemcpyHostToDevice) == cudaSuccess &&
+            cudaMemcpy(dev + 2 * n, z, bytes, cudaMemcpyHostToDevice) == cudaSuccess;
+  if (ok) {
+    fm_density_points<<<(unsigned)((n + 255) / 256), 256>>>(make_density(rho), n, dev, dev + n, dev + 2 * n, dev + 3 * n);
+    ok = cudaMemcpy(out, dev + 3 * n, bytes, cudaMemcpyDeviceToHost) == cudaSuccess;
+  }
+  cudaFree(dev);
+  if (!ok) snprintf(g_create_err, sizeof g_create_err, "fm_density_eval: %s", cudaGetErrorString(cudaGetLastError()));
+  return ok ? 0 : 1;
 }
 
 extern "C" int fm_host_alloc(size_t bytes, void** out) {

@@ -42,6 +42,17 @@ def _d(a):
     return a.ctypes.data_as(C.POINTER(C.c_double))
 
 
+def density_eval(rho, xyz):
+    """rho at the rows of xyz (unit vectors), evaluated on the device by the Lloyd kernel's own
+    density code (fm_density_eval)."""
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+    c = [np.ascontiguousarray(xyz[:, k]) for k in range(3)]
+    out = np.empty(len(xyz))
+    if _lib.lib().fm_density_eval(C.byref(rho), len(xyz), _d(c[0]), _d(c[1]), _d(c[2]), _d(out)):
+        raise FishmanError(_lib.lib().fm_last_error(None).decode())
+    return out
+
+
 def _i(a):
     return a.ctypes.data_as(C.POINTER(C.c_int32))
 

@@ -44,6 +44,12 @@ typedef struct fm_density {
   double cx, cy, cz, beta, alpha, gamma;
 } fm_density;
 
+/* rho at n unit vectors, evaluated on the device by the code the Lloyd kernel uses (host
+ * pointers in and out; no mesh needed).  For diagnostics and for the parity tests of the
+ * density function itself. */
+int fm_density_eval(const fm_density* rho, int64_t n, const double* x, const double* y, const double* z,
+                    double* out);
+
 /* delaunay_voronoi_init(num_point, x=, y=, z=)  DV:188-224.  Copies the n generators to
  * the device (contiguous arrays: the shim packs strided sections first), orders them
  * along a space-filling curve internally and rejects duplicate points (DV:286-288). */

@@ -931,6 +931,13 @@ static double density_eval(const fo_density *rho, double x, double y, double z) 
   }
 }
 
+/* rho at n unit vectors (for the parity tests of the density function itself) */
+void fo_density_eval(const fo_density *rho, long long n, const double *x, const double *y, const double *z,
+                     double *out) {
+  long long i;
+  for (i = 0; i < n; i++) out[i] = density_eval(rho, x[i], y[i], z[i]);
+}
+
 /* degree-5, 7-point symmetric rule on the triangle (Radon) */
 static const double QA1 = 0.10128650732345633880, QB1 = 0.79742698535308732240;
 static const double QA2 = 0.47014206410511508977, QB2 = 0.05971587178976982045;

@@ -50,6 +50,15 @@ def density_x4(lon_deg=0.0, lat_deg=40.0, beta=np.pi / 6, alpha=np.pi / 20, gamm
 _lib = None
 
 
+def density_eval(rho, xyz):
+    """rho at the rows of xyz (unit vectors): the oracle's density_eval"""
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+    c = [np.ascontiguousarray(xyz[:, k]) for k in range(3)]
+    out = np.empty(len(xyz))
+    lib().fo_density_eval(C.byref(rho), len(xyz), _d(c[0]), _d(c[1]), _d(c[2]), _d(out))
+    return out
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -73,6 +82,8 @@ def lib():
         L.fo_get_generators.argtypes = [vp, dp, dp, dp]
         L.fo_set_generators.argtypes = [vp, dp, dp, dp]
         L.fo_centroids.argtypes = [vp, C.POINTER(Density), dp, dp, dp]
+        L.fo_density_eval.restype = None
+        L.fo_density_eval.argtypes = [C.POINTER(Density), C.c_longlong, dp, dp, dp, dp]
         L.fo_lloyd_step.argtypes = [vp, C.POINTER(Density), C.c_int, C.c_int, C.c_int, dp]
         L.fo_calc_area.restype = C.c_double
         L.fo_calc_area.argtypes = [C.c_int, dp, dp, dp]
