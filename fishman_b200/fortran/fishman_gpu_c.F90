@@ -22,7 +22,7 @@ module fishman_gpu_c
   public :: fm_voronoi, fm_get_circumcentres, fm_get_rings, fm_get_edges
   public :: fm_mpas, fm_get_mpas_edges, fm_get_mpas_cells, fm_get_mpas_vertices, fm_get_mpas_edges_on_edge
   public :: fm_lloyd, fm_lloyd_local, fm_generator_block, fm_peer_handle, fm_peer_attach
-  public :: fm_get_generators, fm_set_generators
+  public :: fm_get_generators, fm_set_generators, fm_density_eval
   public :: fm_error_message
 
   ! typedef struct fm_density { int32_t kind; double cx, cy, cz, beta, alpha, gamma; }
@@ -172,6 +172,15 @@ module fishman_gpu_c
       integer(c_int32_t), value :: warm
       real(c_double), intent(out) :: max_disp
     end function fm_lloyd_local
+
+    ! rho at n unit vectors, evaluated by the device code of the Lloyd kernel (diagnostics)
+    integer(c_int) function fm_density_eval(rho, n, x, y, z, out) bind(C, name='fm_density_eval')
+      import :: c_int, c_int64_t, c_double, fm_density
+      type(fm_density), intent(in) :: rho
+      integer(c_int64_t), value :: n
+      real(c_double), intent(in) :: x(*), y(*), z(*)
+      real(c_double), intent(out) :: out(*)
+    end function fm_density_eval
 
     integer(c_int) function fm_generator_block(h, d_records, n_padded, begin, count) &
         bind(C, name='fm_generator_block')
