@@ -10,6 +10,8 @@
 //   Backend::fill64(ptr, value, count)    device memset of 64-bit words
 //   Backend::fill32(ptr, value, count)
 //   Backend::exclusive_scan(ptr, n)       in place over ints; returns the total
+//   Backend::launch_counted<K>(ctx, idx, upper)  K::run(ctx, i) for i in [0, counters[idx]), a count the host
+//                                         only knows an upper bound of
 //   Backend::read_ints(dst, src, n)       device -> host (synchronising)
 //   Backend::write_ints(dst, src, n)      host -> device
 //   Backend::argmax_dot(ctx, d)           index of the point with the largest p . d
@@ -182,10 +184,11 @@ int dt_flip_loop_host(B& be, DtCtx& c, int* list[2], int cur, bool skip_check, i
     if (!skip_check) be.template launch_filtered<KCheckT>(c, nact);
     skip_check = false;
     be.template launch<KMark>(c, nact);
-    be.template launch<KFlip>(c, nact);
-    be.template launch<KPatch>(c, nact);
+    be.template launch_counted<KFlip>(c, FM_C_NFLIP, nact);
+    be.template launch_counted<KPatch>(c, FM_C_NFLIP, nact);
     int zero = 0;
     be.write_ints(c.counters + cur, &zero, 1);
+    be.write_ints(c.counters + FM_C_NFLIP, &zero, 1);
     (*stamp)++;
     cur ^= 1;
     if (*stamp > (1 << 28)) {

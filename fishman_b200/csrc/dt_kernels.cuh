@@ -58,6 +58,7 @@ static const u64 kNone64 = ~0ULL;
 // slots of DtCtx::counters (16 ints; [0..14] are cleared together at the start of a build or
 // repair, the stamp survives)
 enum {
+  FM_C_NFLIP = 7,      // pairs marked for a flip in the current sub-round = entries of DtCtx::fliplist
   FM_C_SLOW = 8,       // deferred items of a filtered launch
   FM_C_SLOWDONE = 9,   // blocks of the deferred kernel that have finished (self-reset)
   FM_C_MAXDISP = 10,   // 64-bit word: bits of the largest chord displacement ([10], [11])
@@ -111,6 +112,8 @@ struct DtCtx {
   const int* active;           // triangles to check this sub-round
   int n_active;
   int* next_active;            // queue for the next sub-round
+  int* fliplist;               // the winners of the current sub-round's votes (KMark), compact:
+                               // KFlip and KPatch run over these instead of the whole queue
   int* qcount;                 // length of next_active (one of counters[0], counters[1])
   int* counters;               // [0],[1] queue lengths (ping-pong), [2] flips, [3] turned-over
                                // triangles, [4] splits, [5] flip sub-rounds, [6] largest queue,
@@ -498,6 +501,10 @@ struct KMark {
     if (c.vote[t] == key && c.vote[n] == key) {
       c.role[t] = (c.stamp << 2) | 1;
       c.role[n] = (c.stamp << 2) | 2;
+      // Only a fraction of the queue flips (measured: 6 of 32 lanes in a late insertion round);
+      // one thread per queue entry would run the flip's chain of dependent gathers in nearly
+      // empty warps.  The winners go on a compact list instead.
+      c.fliplist[FM_ATOMIC_ADD32(&c.counters[FM_C_NFLIP], 1)] = t;
     } else {
       queue_active(c, t, c.stamp + 1);  // lost the vote: try again next sub-round
     }
@@ -526,10 +533,9 @@ FM_HD inline FlipGeom flip_geom(int t, int k, int n, int e) {
   return g;
 }
 
-struct KFlip {
+struct KFlip {   // over fliplist[0 .. counters[FM_C_NFLIP])
   FM_HD static void run(const DtCtx& c, int i) {
-    int t = c.active[i];
-    if (c.role[t] != ((c.stamp << 2) | 1)) return;
+    int t = c.fliplist[i];
     int k = c.flip_edge[t];
     Row rt = c.row[t];
     I4 vt = rt.v, at = rt.a;
@@ -575,10 +581,9 @@ struct KFlip {
 // After all flips of the sub-round: a pair whose outer neighbour flipped too
 // finds that neighbour's new (slot, edge) in the mailbox of its OLD (slot, edge).
 // The pre-flip indices come back from flip_edge[t] (k) and row[t].v.w (e).
-struct KPatch {
+struct KPatch {  // over fliplist[0 .. counters[FM_C_NFLIP])
   FM_HD static void run(const DtCtx& c, int i) {
-    int t = c.active[i];
-    if (c.role[t] != ((c.stamp << 2) | 1)) return;
+    int t = c.fliplist[i];
     int k = c.flip_edge[t];
     int n = c.row[t].a.y >> 2;
     int e = c.row[t].v.w;

@@ -75,7 +75,7 @@ struct fm_handle {
   // triangulation
   Row* rows = nullptr;
   int *loc = nullptr, *rankbuf = nullptr, *flip_edge = nullptr, *role = nullptr, *amark = nullptr;
-  int *listA = nullptr, *listB = nullptr, *counters = nullptr, *err = nullptr, *v2t = nullptr;
+  int *listA = nullptr, *listB = nullptr, *fliplist = nullptr, *counters = nullptr, *err = nullptr, *v2t = nullptr;
   u64 *winner = nullptr, *vote = nullptr, *mailbox = nullptr, *scratch64 = nullptr;
   void* cub_tmp = nullptr;
   size_t cub_bytes = 0;
@@ -198,7 +198,7 @@ struct fm_handle {
     c.n = n; c.pts = pts; c.v2t = v2t; c.ringc = ringc; c.row = rows; c.loc = loc;
     c.winner = winner; c.rank = rankbuf; c.n_tri = n_tri; c.stamp = stamp; c.stamp_dev = counters + FM_C_STAMP;
     c.vote = vote; c.flip_edge = flip_edge; c.role = role; c.mailbox = mailbox; c.amark = amark;
-    c.counters = counters; c.qcount = counters; c.err = err; c.slow = rankbuf;
+    c.counters = counters; c.qcount = counters; c.err = err; c.slow = rankbuf; c.fliplist = fliplist;
     static const int pf_waves = getenv("FM_PREFETCH_WAVES") ? atoi(getenv("FM_PREFETCH_WAVES")) : 1;
     c.pf_dist = pf_waves * sms * 4 * 256;  // the sweep runs 4 blocks of 256 per SM: one wave ahead
     return c;
@@ -223,6 +223,15 @@ struct CudaBackend {
   fm_handle* h;
   template <class K>
   void launch(const DtCtx& c, int n) { h->launch<K, DtCtx>(c, n); }
+  // K over [0, counters[idx]); `upper` bounds the count (threads past it leave after one load)
+  template <class K>
+  void launch_counted(const DtCtx& c, int idx, int upper) {
+    if (upper <= 0) return;
+    h->prof_begin();
+    fm_kernel_counted<K><<<(upper + 255) / 256, 256, 0, h->stream>>>(c, idx);
+    h->note_cuda(cudaGetLastError(), KName<K>::get());
+    h->prof_end(KName<K>::get(), upper);
+  }
   // filter-only kernel over [0, n), then the exact kernel over what it deferred
   template <template <bool> class K>
   void launch_filtered(const DtCtx& c, int n) {
@@ -328,8 +337,8 @@ struct CudaBackend {
       if (!skip_check) launch_filtered<KCheckT>(c, nact);
       skip_check = false;
       launch<KMark>(c, nact);
-      launch<KFlip>(c, nact);
-      launch<KPatch>(c, nact);
+      launch_counted<KFlip>(c, FM_C_NFLIP, nact);  // winners are queue entries: at most nact (and, being disjoint pairs, T / 2)
+      launch_counted<KPatch>(c, FM_C_NFLIP, nact);
       fm_subround_end<<<1, 1, 0, h->stream>>>(c.counters, cur, nact);
       cur ^= 1;
       read_ints(&nact, c.counters + cur, 1);
@@ -442,7 +451,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n));
   A(dalloc(&h->rows, T));
   A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
-  A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T));
+  A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T)); A(dalloc(&h->fliplist, T / 2 + 1));
   A(dalloc(&h->counters, 16));
   h->err = h->counters + FM_C_ERR;
   A(dalloc(&h->winner, T)); A(dalloc(&h->vote, T)); A(dalloc(&h->mailbox, 3 * T)); A(dalloc(&h->scratch64, 4));
@@ -547,7 +556,7 @@ extern "C" void fm_destroy(fm_handle* h) {
       if (p) cudaFree(p);
   }
   void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->rankbuf, h->flip_edge,
-                  h->role, h->amark, h->listA, h->listB, h->counters, h->winner, h->vote,
+                  h->role, h->amark, h->listA, h->listB, h->fliplist, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
   for (void* p : ptrs)
@@ -895,6 +904,7 @@ extern "C" int fm_mpas(fm_handle* h, int32_t strict, int32_t* max_edges) {
   Readback r;
   if (readback(h, &r, "fm_mpas")) return 1;
   int me = r.counters[7];
+  FM_CUDA(cudaMemsetAsync(h->counters + 7, 0, sizeof(int), h->stream));  // slot 7 is FM_C_NFLIP in the flip rounds
   if (me < 3 || me > 4096) { h->fail("fm_mpas: bad largest cell degree %d", me); return 1; }
   if (me > m.cap_max_edges) {
     if (m.eoe) { cudaFree(m.eoe); cudaFree(m.weights); m.eoe = nullptr; m.weights = nullptr; }

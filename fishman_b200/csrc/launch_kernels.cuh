@@ -32,6 +32,13 @@ __global__ void __launch_bounds__(256, KOcc<K>::value) fm_kernel(Ctx c, int n) {
   use_device_stamp(c);
   if (i < n) K::run(c, i);
 }
+// K over [0, counters[idx]): the count lives on the device, the host launches for an upper bound
+template <class K>
+__global__ void __launch_bounds__(256) fm_kernel_counted(DtCtx c, int idx) {
+  use_device_stamp(c);
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < c.counters[idx]) K::run(c, i);
+}
 
 // Second half of a filtered launch: the exact body over the deferred items (grid-stride;
 // the count is only known on the device).
@@ -77,10 +84,14 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
     skip_check = 0;
     for (int i = gid; i < nact; i += gsz) KMark::run(c, i);
     grid.sync();
-    for (int i = gid; i < nact; i += gsz) KFlip::run(c, i);
+    const int nflip = vc[FM_C_NFLIP];  // the winners, compact (KMark)
+    for (int i = gid; i < nflip; i += gsz) KFlip::run(c, i);
     grid.sync();
-    for (int i = gid; i < nact; i += gsz) KPatch::run(c, i);
-    if (gid == 0) c.counters[cur] = 0;  // consumed (every thread read it before the first barrier)
+    for (int i = gid; i < nflip; i += gsz) KPatch::run(c, i);
+    if (gid == 0) {  // consumed: every thread read the two counts right after a barrier
+      c.counters[cur] = 0;
+      c.counters[FM_C_NFLIP] = 0;
+    }
     grid.sync();
     cur ^= 1;
     stamp++;
@@ -95,6 +106,7 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
 // bookkeeping at the end of a host-driven flip sub-round (what thread 0 of fm_flip_coop does)
 __global__ void fm_subround_end(int* counters, int cur, int nact) {
   counters[cur] = 0;
+  counters[FM_C_NFLIP] = 0;
   counters[FM_C_STAMP] += 1;
   counters[5] += 1;
   if (nact > counters[6]) counters[6] = nact;

@@ -18,6 +18,10 @@ struct HostBackend {
   void launch(const DtCtx& c, int n) {
     for (int i = 0; i < n; i++) K::run(c, i);
   }
+  template <class K>
+  void launch_counted(const DtCtx& c, int idx, int /*upper*/) {
+    for (int i = 0, n = c.counters[idx]; i < n; i++) K::run(c, i);
+  }
   // both halves of the filtered-then-exact scheme, as on the device
   template <template <bool> class K>
   void launch_filtered(const DtCtx& c, int n) {
@@ -90,7 +94,7 @@ extern "C" const char* fme_last_error() { return g_err; }
 struct EmuMesh {
   int n = 0, T = 0, stamp = 1, err = 0;
   int counters[16] = {0};
-  std::vector<int> orig, loc, rank, flip_edge, role, amark, listA, listB, v2t, slow;
+  std::vector<int> orig, loc, rank, flip_edge, role, amark, listA, listB, fliplist, v2t, slow;
   std::vector<P4> pts;
   std::vector<Row> row;
   std::vector<u64> winner, vote, mailbox;
@@ -111,13 +115,13 @@ struct EmuMesh {
     for (int i = 0; i < n; i++) pts[i] = P4{xyz[3 * orig[i]], xyz[3 * orig[i] + 1], xyz[3 * orig[i] + 2], orig[i]};
     row.assign(T, Row());
     loc.assign(n, 0); rank.assign(T + 1, 0); flip_edge.assign(T, 0); role.assign(T, 0); amark.assign(T, 0);
-    listA.assign(T, 0); listB.assign(T, 0); v2t.assign(n, -1); slow.assign(T + 1, 0);
+    listA.assign(T, 0); listB.assign(T, 0); fliplist.assign(T / 2 + 1, 0); v2t.assign(n, -1); slow.assign(T + 1, 0);
     winner.assign(T, 0); vote.assign(T, kNone64); mailbox.assign(3 * (size_t)T, 0);
     memset(&c, 0, sizeof c);
     c.n = n; c.pts = pts.data(); c.v2t = v2t.data();
     c.row = row.data(); c.loc = loc.data(); c.winner = winner.data();
     c.rank = rank.data(); c.vote = vote.data(); c.flip_edge = flip_edge.data(); c.role = role.data();
-    c.mailbox = mailbox.data(); c.amark = amark.data(); c.counters = counters; c.err = &err; c.slow = slow.data();
+    c.mailbox = mailbox.data(); c.amark = amark.data(); c.fliplist = fliplist.data(); c.counters = counters; c.err = &err; c.slow = slow.data();
     int boot[4];
     if (dt_bootstrap(be, c, boot, g_err, sizeof g_err)) return 1;
     for (int k = 0; k < 4; k++) loc[boot[k]] = -1;
