@@ -252,7 +252,8 @@ struct KLevelInit {
     int p = c.plist[i];
     if (c.loc[p] < 0) return;  // a bootstrap vertex
     int j = c.prev[p];
-    c.loc[p] = j >= 0 ? c.v2t[j] : 0;
+    // j may itself still be waiting (carried over from its level): then start where ITS walk stands
+    c.loc[p] = j < 0 ? 0 : (c.loc[j] < 0 ? c.v2t[j] : c.loc[j]);
   }
 };
 
