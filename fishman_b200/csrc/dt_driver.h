@@ -224,13 +224,16 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
   int boot_class[4];
   for (int k = 0; k < 4; k++) boot_class[k] = point_class(be.fetch_orig(c, boot[k]), K);
   c.level_max = K;
-  // A level is not driven to completion: after kRoundsPerLevel insertion rounds (one) the points
-  // that lost their vote -- about half of a level -- are carried into the next level, which is
-  // four times larger and whose first round is a big one anyway.  Finishing each level on its
-  // own took six rounds per level, most of them nearly empty and each with the fixed cost of a
-  // round (seven launches, one host read, at least two flip sub-rounds): 48 rounds at 2.6M
-  // points against 22 now.  Only the last level runs dry.  Measured at 2.6M points, rounds per
-  // level 1 / 2 / 3 / 4: 14.8 / 16.0 / 16.9 / 18.1 ms per build (until dry: 19.7 ms).
+  // A level is not driven to completion.  A round inserts at most one point per triangle, so
+  // the mesh can only triple per round and a level four times the size of what is already
+  // there saturates: most of its points lose their vote.  After kRoundsPerLevel rounds (one)
+  // the losers are carried into the next level and vote again there; only the last level runs
+  // dry.  In effect every round inserts about as many points as there are triangles, the
+  // early levels merely keep the number of WALKING points near that number.  Driving each
+  // level dry took 48 rounds at 2.6M points (six per level, most of them nearly empty, each
+  // with the fixed cost of a round: seven launches, one host read, two or more flip
+  // sub-rounds) against 22 now (log3 of the triangle count is 13).  Measured at 2.6M points,
+  // rounds per level 1 / 2 / 3 / 4: 14.8 / 16.0 / 16.9 / 18.1 ms per build (until dry: 19.7).
   static const int kRoundsPerLevel = [] {  // FM_ROUNDS_PER_LEVEL: tuning switch
     const char* e = getenv("FM_ROUNDS_PER_LEVEL");
     int v = e ? atoi(e) : 1;
@@ -275,6 +278,9 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
       c.next_active = list[0];
       c.qcount = c.counters;
       be.template launch<KSplit>(c, c.n_tri);
+      if (getenv("FM_DEBUG_ROUNDS"))
+        fprintf(stderr, "level %d round %d: voters %d pool %d inserted %d triangles %d\n", L, rounds_here, m,
+                remaining, nsplit, c.n_tri);
       remaining -= nsplit;
       c.n_tri += 2 * nsplit;
       if (be.flip_loop(c, list, 0, false, stamp, st, msg, msglen, 3 * nsplit)) return 1;
