@@ -203,7 +203,7 @@ int dt_flip_loop_host(B& be, DtCtx& c, int* list[2], int cur, bool skip_check, i
 // Number of coarseness classes above the finest one: the coarsest level holds ~<= 256 points.
 inline int dt_level_count(int n) {
   int K = 0;
-  while (K < 12 && ((long long)256 << (2 * K)) < n) K++;
+  while (K < 24 / FM_LEVEL_LOG2 && ((long long)256 << (FM_LEVEL_LOG2 * K)) < n) K++;
   return K;
 }
 

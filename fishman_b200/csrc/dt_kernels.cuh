@@ -241,8 +241,13 @@ FM_HD inline int clz32(unsigned v) {
   return n;
 #endif
 }
+#ifndef FM_LEVEL_LOG2
+#define FM_LEVEL_LOG2 2   // log2 of the growth factor between insertion levels (2: levels grow x4).  x2 levels
+                          // (1) need the same 22 rounds at 2.6M points and a third of the walks, but measured
+                          // 17.1 ms per build against 14.9: locate_vote 3.3 ms instead of 1.5
+#endif
 FM_HD inline int point_class(long long id, int K) {
-  int c = clz32(hash32((unsigned)id ^ 0x9e3779b9u)) >> 1;
+  int c = clz32(hash32((unsigned)id ^ 0x9e3779b9u)) / FM_LEVEL_LOG2;
   return c < K ? c : K;
 }
 
