@@ -101,3 +101,39 @@ def test_sharded_point_location_gives_the_same_build(nranks):
     tri1, adj1, _ = _emu.triangulate(p)
     tri, adj = _emu.triangulate_sharded(p, nranks)
     assert np.array_equal(tri, tri1) and np.array_equal(adj, adj1)
+
+
+def test_topology_does_not_depend_on_the_round_schedule(tmp_path):
+    """dt_run carries the points that lost their vote into the next insertion level after
+    FM_ROUNDS_PER_LEVEL rounds (default 1).  The schedule changes which slot a triangle lands in,
+    never the triangulation: one round per level, three, and "until dry" (the schedule before
+    the carry-over) must give the same canonical triangles, on a random set and on a
+    degenerate one (cocircular points of a lat-lon grid, decided by SoS).  The switch is read
+    once per process, hence the subprocesses."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "from tests import _emu, _check\n"
+        "from fishman_b200 import points\n"
+        "lon, lat = np.meshgrid(np.linspace(0, 2 * np.pi, 40, endpoint=False), np.linspace(-1.3, 1.3, 21))\n"
+        "grid = np.c_[(np.cos(lat) * np.cos(lon)).ravel(), (np.cos(lat) * np.sin(lon)).ravel(), np.sin(lat).ravel()]\n"
+        "out = []\n"
+        "for p in (points.uniform(20000, 11), grid):\n"
+        "    tri, adj = _emu.triangulate(p)[:2]\n"
+        "    _check.check_triangulation(p, tri, adj)\n"
+        "    out.append(_check.canonical(tri))\n"
+        "np.savez(sys.argv[1], a=out[0], b=out[1])\n" % root)
+    got = {}
+    for rounds in ("1", "3", "1000"):
+        path = str(tmp_path / f"tri_{rounds}.npz")
+        env = dict(os.environ, FM_ROUNDS_PER_LEVEL=rounds)
+        r = subprocess.run([sys.executable, "-c", script, path], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        with np.load(path) as f:
+            got[rounds] = (f["a"].copy(), f["b"].copy())
+    for rounds in ("3", "1000"):
+        assert np.array_equal(got["1"][0], got[rounds][0])
+        assert np.array_equal(got["1"][1], got[rounds][1])
