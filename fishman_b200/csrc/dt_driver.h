@@ -18,7 +18,8 @@
 //   Backend::fetch_point(ctx, i)          coordinates of point i on the host
 //   Backend::fetch_orig(ctx, i)
 //   Backend::write_tris(ctx, t0, cnt, tri, adj)
-//   Backend::prev_coarser(ctx, thr, prev) prev[i] = largest j <= i with point_class(j) > thr, or -1
+//   Backend::prev_coarser(ctx, thr, prev) prev[i] = largest j <= i with point_class(j) > thr, or -1; returns
+//                                         DtCtx::next_rev (the same to the right, reversed) or null
 //   Backend::flip_loop(ctx, list, cur, skip_check, stamp, stats, msg, len, nact_hint)
 //                                         flip sub-rounds until the queue is empty; nact_hint =
 //                                         length of the first queue when the host knows it, else -1
@@ -249,8 +250,8 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
     if (L > 0 && remaining > 0) {  // start every walk of this level's points next to an already placed point
       c.plist = lvl_order + lvl_off[L];
       c.n_plist = m;
-      be.prev_coarser(c, K - L, prev);
       c.prev = prev;
+      c.next_rev = be.prev_coarser(c, K - L, prev);  // fills prev[]; returns the right-hand array or null
       be.template launch<KLevelInit>(c, m);
     }
     // the voters: this level, and with leftovers all levels before it (inserted points leave at once)
@@ -278,9 +279,15 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
       c.next_active = list[0];
       c.qcount = c.counters;
       be.template launch<KSplit>(c, c.n_tri);
-      if (getenv("FM_DEBUG_ROUNDS"))
-        fprintf(stderr, "level %d round %d: voters %d pool %d inserted %d triangles %d\n", L, rounds_here, m,
+      if (getenv("FM_DEBUG_ROUNDS")) {
+        fprintf(stderr, "level %d round %d: voters %d pool %d inserted %d triangles %d", L, rounds_here, m,
                 remaining, nsplit, c.n_tri);
+#if defined(FM_COUNT_STEPS) && !defined(__CUDACC__)
+        fprintf(stderr, "  walks %lld visited %lld long %lld", fm_walk_stats[1], fm_walk_stats[0], fm_walk_stats[2]);
+        fm_walk_stats[0] = fm_walk_stats[1] = fm_walk_stats[2] = 0;
+#endif
+        fprintf(stderr, "\n");
+      }
       remaining -= nsplit;
       c.n_tri += 2 * nsplit;
       if (be.flip_loop(c, list, 0, false, stamp, st, msg, msglen, 3 * nsplit)) return 1;

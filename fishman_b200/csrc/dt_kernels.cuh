@@ -95,6 +95,8 @@ struct DtCtx {
   int n_plist;
   int locate_only;             // sharded point location: walk and record loc[], the votes are cast later (KVote)
   const int* prev;             // per point: nearest point to the left (internal order) of a coarser level
+  const int* next_rev;         // the same to the right, stored reversed: next_rev[n-1-i] = n-1-j for the
+                               // smallest j >= i of a coarser level, or -1 (null = left side only)
   int level_thr;               // coarseness of the current level
   int level_max;               // coarsest class K
   u64* winner;                 // per triangle: min over its points of (priority << 32 | point)
@@ -243,8 +245,9 @@ FM_HD inline int clz32(unsigned v) {
 }
 #ifndef FM_LEVEL_LOG2
 #define FM_LEVEL_LOG2 2   // log2 of the growth factor between insertion levels (2: levels grow x4).  x2 levels
-                          // (1) need the same 22 rounds at 2.6M points and a third of the walks, but measured
-                          // 17.1 ms per build against 14.9: locate_vote 3.3 ms instead of 1.5
+                          // (1) need the same number of rounds and a third of the walk steps, and measure
+                          // the same: 14.74 against 14.69 ms per build at 2.6M points (with the one-sided
+                          // walk start they were slower, 17.1 ms: ~800 walks of > 30 triangles per build)
 #endif
 FM_HD inline int point_class(long long id, int K) {
   int c = clz32(hash32((unsigned)id ^ 0x9e3779b9u)) / FM_LEVEL_LOG2;
@@ -257,11 +260,27 @@ struct KLevelInit {
     int p = c.plist[i];
     if (c.loc[p] < 0) return;  // a bootstrap vertex
     int j = c.prev[p];
+    if (c.next_rev) {
+      // The curve neighbour on ONE side can be far away in space (the curve jumps between
+      // octants); the nearer of the two sides almost never is.  The few points that started far
+      // away used to set the duration of the whole locate launch with walks of > 30 triangles.
+      int r = c.next_rev[c.n - 1 - p];
+      int jr = r >= 0 ? c.n - 1 - r : -1;
+      if (j < 0) {
+        j = jr;
+      } else if (jr >= 0) {
+        const P4 q = c.pts[p], a = c.pts[j], b = c.pts[jr];
+        if (q.x * b.x + q.y * b.y + q.z * b.z > q.x * a.x + q.y * a.y + q.z * a.z) j = jr;
+      }
+    }
     // j may itself still be waiting (carried over from its level): then start where ITS walk stands
     c.loc[p] = j < 0 ? 0 : (c.loc[j] < 0 ? c.v2t[j] : c.loc[j]);
   }
 };
 
+#if defined(FM_COUNT_STEPS) && !defined(__CUDACC__)
+static long long fm_walk_stats[3];  // triangles visited, walks, walks longer than 30 steps
+#endif
 template <bool EXACT>
 struct KLocateVoteT {
   FM_HD static void run(const DtCtx& c, int i) {
@@ -292,10 +311,8 @@ struct KLocateVoteT {
       if (++steps > (1 << 20)) { *c.err |= FM_E_WALK; return; }
     }
     c.loc[p] = t;
-#ifdef FM_COUNT_STEPS
-    FM_ATOMIC_ADD32(&c.counters[12], steps + 1);
-    FM_ATOMIC_ADD32(&c.counters[13], 1);
-    if (steps > 30) FM_ATOMIC_ADD32(&c.counters[14], 1);
+#if defined(FM_COUNT_STEPS) && !defined(__CUDACC__)  // host emulation only: walk statistics
+    fm_walk_stats[0] += steps + 1; fm_walk_stats[1] += 1; fm_walk_stats[2] += steps > 30;
 #endif
     if (c.locate_only) return;
     u64 key = ((u64)hash32((unsigned)qi) << 32) | (unsigned)p;

@@ -69,7 +69,7 @@ struct fm_handle {
   int *orig = nullptr, *inv = nullptr;
   int* ringc = nullptr;  // ring cache of the Lloyd kernel: 8 ints per vertex
   // insertion levels: points sorted by (level, internal index), level offsets (host), scratch
-  int *lvl_order = nullptr, *prev = nullptr;
+  int *lvl_order = nullptr, *prev = nullptr, *next_rev = nullptr;
   int lvl_K = 0;
   std::vector<int> lvl_off;
   // triangulation
@@ -302,12 +302,16 @@ struct CudaBackend {
   struct MaxOp {
     __host__ __device__ int operator()(int a, int b) const { return a > b ? a : b; }
   };
-  void prev_coarser(const DtCtx& c, int thr, int* prev) {
+  const int* prev_coarser(const DtCtx& c, int thr, int* prev) {
     h->prof_begin();
-    fm_prev_keys<<<(c.n + 255) / 256, 256, 0, h->stream>>>(c.n, c.pts, c.level_max, thr, prev);
+    fm_prev_keys<<<(c.n + 255) / 256, 256, 0, h->stream>>>(c.n, c.pts, c.level_max, thr, prev, h->next_rev);
     size_t bytes = h->cub_bytes;
     h->note_cuda(cub::DeviceScan::InclusiveScan(h->cub_tmp, bytes, prev, prev, MaxOp(), c.n, h->stream), "prev scan");
+    bytes = h->cub_bytes;
+    h->note_cuda(cub::DeviceScan::InclusiveScan(h->cub_tmp, bytes, h->next_rev, h->next_rev, MaxOp(), c.n, h->stream),
+                 "next scan");
     h->prof_end("prev_coarser", c.n);
+    return h->next_rev;
   }
   void write_tris(const DtCtx& c, int t0, int cnt, const I4* tri, const I4* adj) {
     std::vector<Row> rows(cnt);
@@ -448,7 +452,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
     A(cudaMalloc((void**)&h->ringc, 32 * (size_t)n));
     A(cudaMemsetAsync(h->ringc, 0xff, 32 * (size_t)n, h->stream));
   }
-  A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n));
+  A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n)); A(dalloc(&h->next_rev, n));
   A(dalloc(&h->rows, T));
   A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T)); A(dalloc(&h->fliplist, T / 2 + 1));
@@ -555,7 +559,7 @@ extern "C" void fm_destroy(fm_handle* h) {
     for (void* p : mptrs)
       if (p) cudaFree(p);
   }
-  void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->rows, h->rankbuf, h->flip_edge,
+  void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->next_rev, h->rows, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->fliplist, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};

@@ -337,9 +337,13 @@ __global__ void fm_level_offsets(int n, const unsigned* sorted_key, int K, int* 
   }
   off[L] = lo;
 }
-__global__ void fm_prev_keys(int n, const P4* pts, int K, int thr, int* prev) {
+__global__ void fm_prev_keys(int n, const P4* pts, int K, int thr, int* prev, int* next_rev) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) prev[i] = point_class(pts[i].id, K) > thr ? i : -1;
+  if (i < n) {
+    bool coarser = point_class(pts[i].id, K) > thr;
+    prev[i] = coarser ? i : -1;
+    next_rev[n - 1 - i] = coarser ? n - 1 - i : -1;  // max-scan of the reversed order = nearest to the right
+  }
 }
 
 __global__ void fm_morton_keys(int n, const double* x, const double* y, const double* z, u64* key,

@@ -73,12 +73,20 @@ struct HostBackend {
       c.v2t[tri[i].x] = c.v2t[tri[i].y] = c.v2t[tri[i].z] = t0 + i;
     }
   }
-  void prev_coarser(const DtCtx& c, int thr, int* prev) {
+  std::vector<int> next_rev;
+  const int* prev_coarser(const DtCtx& c, int thr, int* prev) {
     int last = -1;
     for (int i = 0; i < c.n; i++) {
       if (point_class(c.pts[i].id, c.level_max) > thr) last = i;
       prev[i] = last;
     }
+    next_rev.assign(c.n, -1);
+    last = -1;
+    for (int r = 0; r < c.n; r++) {  // r = n-1-i: the same scan over the reversed order
+      if (point_class(c.pts[c.n - 1 - r].id, c.level_max) > thr) last = r;
+      next_rev[r] = last;
+    }
+    return next_rev.data();
   }
   int flip_loop(DtCtx& c, int* list[2], int cur, bool skip_check, int* stamp, DtStats* st, char* msg,
                 size_t msglen, int) {
