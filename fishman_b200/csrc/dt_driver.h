@@ -20,6 +20,8 @@
 //   Backend::write_tris(ctx, t0, cnt, tri, adj)
 //   Backend::prev_coarser(ctx, thr, prev) prev[i] = largest j <= i with point_class(j) > thr, or -1; returns
 //                                         DtCtx::next_rev (the same to the right, reversed) or null
+//   Backend::bump_stamp(stamp)            advance the sub-round stamp past every value in use (host mirror
+//                                         *stamp, or the device-resident counters[FM_C_STAMP])
 //   Backend::flip_loop(ctx, list, cur, skip_check, stamp, stats, msg, len, nact_hint)
 //                                         flip sub-rounds until the queue is empty; nact_hint =
 //                                         length of the first queue when the host knows it, else -1
@@ -222,6 +224,11 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
   int zero[15] = {0}, host[8];
   int* list[2] = {listA, listB};
   be.write_ints(c.counters, zero, 15);
+  // Every build starts on a stamp newer than anything left in amark / vote / role / mailbox.  A
+  // warm repair that found a turned-over triangle has stamped amark[] and vote[] with the
+  // current stamp and left (the flip loop returns at once without advancing it); a rebuild on
+  // that same stamp would find its freshly split triangles "already queued" and never check them.
+  be.bump_stamp(stamp);
   int boot_class[4];
   for (int k = 0; k < 4; k++) boot_class[k] = point_class(be.fetch_orig(c, boot[k]), K);
   c.level_max = K;

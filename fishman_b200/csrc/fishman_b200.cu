@@ -247,6 +247,10 @@ struct CudaBackend {
   // then every rank casts all votes -- the triangulation stays replicated and identical.  Small
   // levels are not worth the exchange and are located whole on every rank.
   void locate_round(DtCtx& c, int m);
+  void bump_stamp(int*) {  // the stamp lives on the device (counters[FM_C_STAMP]); no host round trip
+    fm_bump_stamp<<<1, 1, 0, h->stream>>>(h->counters, 2);
+    h->note_cuda(cudaGetLastError(), "bump_stamp");
+  }
   void fill64(u64* p, u64 v, size_t n) {
     // only all-ones is ever requested: a byte memset does it
     h->note_cuda(cudaMemsetAsync(p, (int)(v & 0xff), n * sizeof(u64), h->stream), "fill64");
@@ -788,13 +792,6 @@ extern "C" int fm_get_triangles(fm_handle* h, int32_t* tri, int32_t* adj) {
   return 0;
 }
 
-static int bump_stamp(fm_handle* h, int current) {
-  int next = current + 1;
-  FM_CUDA(cudaMemcpyAsync(h->counters + FM_C_STAMP, &next, sizeof(int), cudaMemcpyHostToDevice, h->stream));
-  FM_CUDA(cudaStreamSynchronize(h->stream));
-  return 0;
-}
-
 extern "C" int fm_voronoi(fm_handle* h, int32_t all) {
   if (!h->have_dt) { h->fail("voronoi_diagram before delaunay_triangulation"); return 1; }
   size_t T = (size_t)h->n_tri;
@@ -1090,7 +1087,6 @@ static int lloyd_iteration(fm_handle* h, const fm_density* rho, int warm, double
       *maxdisp = r.maxdisp;
       return 0;
     }
-    if (bump_stamp(h, r.stamp)) return 1;
   }
   if (triangulate_cold(h)) return 1;
   if (circumcentres(h, false)) return 1;

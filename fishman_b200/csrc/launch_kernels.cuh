@@ -103,6 +103,8 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
   }
 }
 
+__global__ void fm_bump_stamp(int* counters, int by) { counters[FM_C_STAMP] += by; }
+
 // bookkeeping at the end of a host-driven flip sub-round (what thread 0 of fm_flip_coop does)
 __global__ void fm_subround_end(int* counters, int cur, int nact) {
   counters[cur] = 0;

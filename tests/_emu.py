@@ -80,3 +80,22 @@ def triangulate_sharded(xyz, nranks):
     if rc:
         raise RuntimeError(lib().fme_last_error().decode())
     return tri, adj
+
+
+def rebuild_after_failed_repair(xyz_old, xyz_new, skip_bump=False):
+    """build(xyz_old), move the points, warm sweep (finds turned-over triangles and leaves), then
+    the in-place rebuild.  Returns (tri, adj, turned).  skip_bump: start the rebuild on the stamp the
+    sweep used (the defect fm_retriangulate(h, warm=1) had)."""
+    a = np.ascontiguousarray(xyz_old, dtype=np.float64)
+    b = np.ascontiguousarray(xyz_new, dtype=np.float64)
+    n = len(a)
+    T = 2 * n - 4
+    tri = np.empty((T, 3), np.int32)
+    adj = np.empty((T, 3), np.int32)
+    turned = C.c_int(0)
+    ip, dp = C.POINTER(C.c_int), C.POINTER(C.c_double)
+    rc = lib().fme_rebuild_after_failed_repair(n, a.ctypes.data_as(dp), b.ctypes.data_as(dp), 1 if skip_bump else 0,
+                                               tri.ctypes.data_as(ip), adj.ctypes.data_as(ip), C.byref(turned))
+    if rc:
+        raise RuntimeError(lib().fme_last_error().decode())
+    return tri, adj, turned.value

@@ -90,8 +90,13 @@ struct HostBackend {
   }
   int flip_loop(DtCtx& c, int* list[2], int cur, bool skip_check, int* stamp, DtStats* st, char* msg,
                 size_t msglen, int) {
+    // as fm_flip_coop on the device: a turned-over triangle leaves everything to the rebuild
+    if (emulate_abort && skip_check && c.counters[3] > 0) return 0;
     return dt_flip_loop_host(*this, c, list, cur, skip_check, stamp, st, msg, msglen);
   }
+  bool emulate_abort = false;
+  bool skip_bump = false;  // test switch: reproduce a rebuild that starts on a used stamp
+  void bump_stamp(int* stamp) { if (!skip_bump) *stamp += 2; }
 };
 
 static char g_err[512];
@@ -125,6 +130,12 @@ struct EmuMesh {
     loc.assign(n, 0); rank.assign(T + 1, 0); flip_edge.assign(T, 0); role.assign(T, 0); amark.assign(T, 0);
     listA.assign(T, 0); listB.assign(T, 0); fliplist.assign(T / 2 + 1, 0); v2t.assign(n, -1); slow.assign(T + 1, 0);
     winner.assign(T, 0); vote.assign(T, kNone64); mailbox.assign(3 * (size_t)T, 0);
+    return run();
+  }
+  // bootstrap + insertion rounds over the current pts[]; callable again after the points moved
+  // (the in-place rebuild of the CUDA handle: nothing but loc[] is reset)
+  int run() {
+    std::fill(loc.begin(), loc.end(), 0);
     memset(&c, 0, sizeof c);
     c.n = n; c.pts = pts.data(); c.v2t = v2t.data();
     c.row = row.data(); c.loc = loc.data(); c.winner = winner.data();
@@ -231,6 +242,31 @@ extern "C" int fme_repair(int n, const double* xyz_old, const double* xyz_new, i
     if (bad == 0 && m.be.flip_loop(c, list, 0, true, &m.stamp, &m.st, g_err, sizeof g_err, -1)) return 1;
   }
   *turned = c.counters[3];
+  if (m.err) { snprintf(g_err, sizeof g_err, "error bits %d", m.err); return 1; }
+  m.export_tris(tri_out, adj_out);
+  return 0;
+}
+
+// A failed warm repair followed by the in-place rebuild (fm_retriangulate(h, warm=1) when a
+// triangle turned over): build(xyz_old), move the points, sweep (which stamps amark[] / vote[]
+// and finds the turned-over triangles; the flip loop then leaves at once, as fm_flip_coop does),
+// then bootstrap + insertion rounds again on the same arrays.  skip_bump = 1 reproduces a
+// rebuild that starts on the stamp the sweep used.
+extern "C" int fme_rebuild_after_failed_repair(int n, const double* xyz_old, const double* xyz_new, int skip_bump,
+                                               int* tri_out, int* adj_out, int* turned) {
+  g_err[0] = 0;
+  EmuMesh m;
+  if (m.build(n, xyz_old, 1)) return 1;
+  for (int i = 0; i < n; i++) {
+    int o = m.orig[i];
+    m.pts[i].x = xyz_new[3 * o]; m.pts[i].y = xyz_new[3 * o + 1]; m.pts[i].z = xyz_new[3 * o + 2];
+  }
+  m.be.emulate_abort = true;
+  if (dt_repair_async(m.be, m.c, m.listA.data(), m.listB.data(), &m.stamp, &m.st, g_err, sizeof g_err)) return 1;
+  *turned = m.c.counters[3];
+  m.err = 0;
+  m.be.skip_bump = skip_bump != 0;
+  if (m.run()) return 1;
   if (m.err) { snprintf(g_err, sizeof g_err, "error bits %d", m.err); return 1; }
   m.export_tris(tri_out, adj_out);
   return 0;

@@ -137,3 +137,29 @@ def test_topology_does_not_depend_on_the_round_schedule(tmp_path):
     for rounds in ("3", "1000"):
         assert np.array_equal(got["1"][0], got[rounds][0])
         assert np.array_equal(got["1"][1], got[rounds][1])
+
+
+@pytest.mark.parametrize("n", [40, 200, 2000])
+def test_rebuild_after_a_failed_warm_repair(n):
+    """fm_retriangulate(h, warm=1) when a triangle turned over: the sweep has stamped amark[] /
+    vote[] with the current stamp, the flip loop left without advancing it, and the rebuild runs on
+    the same arrays.  dt_run must start on a fresh stamp (Backend::bump_stamp), otherwise the slots
+    the sweep marked are taken for "already queued" and their new triangles are never legalised."""
+    differ_without = 0
+    for trial in range(60 if n <= 200 else 6):
+        rng = np.random.default_rng(1000 * n + trial)
+        p = points.uniform(n, trial)
+        q = p + 1.5 * np.sqrt(4 * np.pi / n) * rng.normal(size=p.shape)   # strongly moved
+        q /= np.linalg.norm(q, axis=1)[:, None]
+        fresh = _check.canonical(_emu.triangulate(q)[0])
+        tri, adj, turned = _emu.rebuild_after_failed_repair(p, q)
+        assert turned > 0
+        _check.check_triangulation(q, tri, adj)
+        assert np.array_equal(_check.canonical(tri), fresh)
+        try:
+            bad = _check.canonical(_emu.rebuild_after_failed_repair(p, q, skip_bump=True)[0])
+            differ_without += not np.array_equal(bad, fresh)
+        except RuntimeError:
+            differ_without += 1
+    if n == 40:
+        assert differ_without > 0   # the defect is real: without the bump some rebuilds are not Delaunay
