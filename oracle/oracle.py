@@ -147,6 +147,14 @@ class Oracle:
         lib().fo_get_triangles(self._h, _i(tri), _i(adj))
         return tri, adj
 
+    def triangles(self):
+        """(tri, adj) of the last triangulation (after lloyd_step: the one of the generators the step started from)."""
+        nT = lib().fo_num_triangles(self._h)
+        tri = np.empty((nT, 3), dtype=np.int32)
+        adj = np.empty((nT, 3), dtype=np.int32)
+        lib().fo_get_triangles(self._h, _i(tri), _i(adj))
+        return tri, adj
+
     def voronoi_diagram(self):
         self._chk(lib().fo_voronoi(self._h))
         nT = lib().fo_num_triangles(self._h)

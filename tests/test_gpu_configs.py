@@ -1,6 +1,10 @@
-"""GPU tests (-m gpu) at the sizes BASELINE.json's configs name, through size-independent
-properties (the oracle takes minutes there), plus the multi-GPU consistency check when the box
-has at least two GPUs."""
+"""GPU tests (-m gpu) at the sizes BASELINE.json's configs name: against the CPU oracle with the
+SURVEY 7.4 topology rule (tests/_check.compare_topology: every differing quad must be inside the
+reference's ON_CIRCLE band, DV:878-880) and 1e-12 on circumcentres / generators, plus
+size-independent properties, plus the multi-GPU consistency check when the box has two GPUs.
+
+Tolerances (north_star: 1e-12 relative per iteration; coordinates are unit vectors, so absolute
+= relative): circumcentres and generators 1e-12; max_disp 1e-12 absolute."""
 import os
 import subprocess
 import sys
@@ -69,11 +73,31 @@ def test_c3_655362_variable_density():
     m.retriangulate(warm=True)
     tri, adj = m.triangles()
     _check.check_triangulation(g, tri, adj)
+    # topology by the rule, against the restatement of the reference on the same generators ...
+    from oracle import oracle as O
+    o = O.Oracle(g)
+    otri, _ = o.delaunay_triangulation()
+    r = _check.compare_topology(g, tri, otri, exact_side="a")
+    print("C3 vs oracle: differing triangles", r["n_diff"], r["explained"])
+    # ... and against Qhull (its own merge tolerance): any difference must be a quad inside the band,
+    # and the GPU's diagonal the exactly-Delaunay one (rational arithmetic)
     hull = ConvexHull(g).simplices + 1
-    a, b = _check.canonical(tri), _check.canonical(hull)
-    if not np.array_equal(a, b):   # Qhull merges / splits nearly cocircular quads by its own tolerance
-        sa, sb = set(map(tuple, a.tolist())), set(map(tuple, b.tolist()))
-        assert len(sa ^ sb) <= 8, len(sa ^ sb)
+    rq = _check.compare_topology(g, tri, hull, exact_side="a")
+    print("C3 vs Qhull: differing triangles", rq["n_diff"], rq["explained"])
+    # one more Lloyd step under the x4 density against the oracle, both from g
+    occ = o.voronoi_diagram()[0]
+    m.voronoi_diagram(all=False)
+    cc, _ = m.circumcentres()
+    assert _check.max_rows_diff(cc[r["common_a"]], occ[r["common_b"]]) < 1e-12
+    og = o.centroids(O.density_x4())
+    it, md = m.lloyd(rho, max_iter=1, warm=True)
+    g1 = m.generators()
+    assert np.abs(g1 - og).max() < 1e-12
+    assert abs(md - np.linalg.norm(og - g, axis=1).max()) < 1e-12
+    o.close()
+    g = g1
+    m.retriangulate(warm=True)
+    tri, adj = m.triangles()
     m.voronoi_diagram(all=True)
     mp = m.mpas(strict=False)
     assert mp["maxEdges"] >= 7
@@ -82,6 +106,71 @@ def test_c3_655362_variable_density():
     c = np.array([np.cos(np.deg2rad(40.0)), 0.0, np.sin(np.deg2rad(40.0))])
     d = np.arccos(np.clip(g @ c, -1, 1))
     assert mp["areaCell"][d < 0.3].mean() < mp["areaCell"][d > 1.5].mean()
+    m.close()
+
+
+def test_c2_ico7_lloyd_steps_against_oracle():
+    """configs[1] against the oracle: ICO(7), k = 5 Lloyd steps, both sides re-fed the same
+    generators each step.  Generators and max_disp at 1e-12 every step.  Topology: the
+    symmetric start is all cocircular quads decided by SoS here and by history in the reference --
+    compared by the rule from step 1 on (the relaxed mesh keeps near-symmetric quads: the
+    differences, if any, must all be inside the band)."""
+    import fishman_b200 as fb
+    from fishman_b200 import points
+    from oracle import oracle as O
+    p = points.ico(7)
+    m = fb.Mesh.from_xyz(p)
+    o = O.Oracle(p)
+    rho_g, rho_o = fb.density_uniform(), O.density_uniform()
+    for it in range(5):
+        g0 = m.generators()
+        n_it, md = m.lloyd(rho_g, max_iter=1, warm=True)
+        o.set_generators(g0)
+        omd = o.lloyd_step(rho_o)          # DT + VD of g0, then the centroid update
+        og, g1 = o.generators(), m.generators()
+        assert np.abs(g1 - og).max() < 1e-12, it
+        assert abs(md - omd) < 1e-12, it
+        if it >= 1:
+            otri, _ = o.triangles()
+            m2 = fb.Mesh.from_xyz(g0)      # the triangulation the GPU step was computed on
+            m2.delaunay_triangulation()
+            r = _check.compare_topology(g0, m2.triangles()[0], otri, exact_side="a")
+            print("C2 step", it, "differing triangles", r["n_diff"], r["explained"])
+            m2.close()
+    st = m.stats()
+    assert st["warm"] >= 4
+    m.close(); o.close()
+
+
+def test_c4_2621442_against_oracle():
+    """configs[3], the headline size, against the oracle: one cold Delaunay triangulation + Voronoi
+    vertices + one Lloyd step at 2,621,442 generators (FIB + jitter, randomly permuted so that the
+    reference's index-order insertion is not quadratic; the SAME permuted array on both sides).
+    Topology by the SURVEY 7.4 rule, circumcentres, generators and max_disp at 1e-12."""
+    import fishman_b200 as fb
+    from fishman_b200 import points
+    from oracle import oracle as O
+    n = 2621442
+    p = points.fibonacci(n, 0, 0.2)
+    p = np.ascontiguousarray(p[np.random.default_rng(0).permutation(n)])
+    m = fb.Mesh.from_xyz(p)
+    m.delaunay_triangulation()
+    m.voronoi_diagram(all=False)
+    tri, adj = m.triangles()
+    cc, _ = m.circumcentres()
+    o = O.Oracle(p)
+    otri, _ = o.delaunay_triangulation()
+    occ = o.voronoi_diagram()[0]
+    r = _check.compare_topology(p, tri, otri, exact_side="a")
+    print("C4: differing triangles", r["n_diff"], r["explained"], "oracle band hits", o.stats()["n_incircle_on"])
+    assert _check.max_rows_diff(cc[r["common_a"]], occ[r["common_b"]]) < 1e-12
+    og = o.centroids(O.density_uniform())
+    o.close()
+    it, md = m.lloyd(fb.density_uniform(), max_iter=1, warm=True)
+    g1 = m.generators()
+    assert np.abs(g1 - og).max() < 1e-12
+    assert abs(md - np.linalg.norm(og - p, axis=1).max()) < 1e-12
+    assert m.stats()["warm"] == 1      # the step ran on the triangulation compared above
     m.close()
 
 
