@@ -15,7 +15,20 @@ SYMBOLS = [
     "fm_get_mpas_edges_on_edge", "fm_lloyd", "fm_lloyd_local", "fm_generator_block", "fm_peer_handle", "fm_peer_attach", "fm_density_eval", "fm_get_generators",
     "fm_set_generators", "fm_host_alloc", "fm_host_free", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
     "fm_profile_enable", "fm_profile_get", "fm_device_info",
+    "fm_block_ids", "fm_get_generators_block", "fm_set_generators_block", "fm_quality",
 ]
+
+
+class QualityStats(C.Structure):
+    """fm_quality_stats of include/fishman_b200.h"""
+    _fields_ = [("degree_hist", C.c_int64 * 16)] + [(k, C.c_double) for k in (
+        "area_cell_min", "area_cell_max", "area_cell_sum", "area_tri_min", "area_tri_max", "area_tri_sum",
+        "angle_min", "angle_max", "max_disp")]
+
+    def asdict(self):
+        d = {k: getattr(self, k) for k, _ in self._fields_[1:]}
+        d["degree_hist"] = [int(v) for v in self.degree_hist]
+        return d
 
 
 class Density(C.Structure):
@@ -71,5 +84,9 @@ def lib():
     L.fm_profile_enable.argtypes = [vp, i32]
     L.fm_profile_get.argtypes = [vp, i32, C.c_void_p, i64p, dp, i64p, ip]
     L.fm_device_info.argtypes = [C.c_char_p, i32, ip]
+    L.fm_block_ids.argtypes = [vp, ip]
+    L.fm_get_generators_block.argtypes = [vp, dp, dp, dp]
+    L.fm_set_generators_block.argtypes = [vp, dp, dp, dp]
+    L.fm_quality.argtypes = [vp, C.POINTER(Density), C.POINTER(QualityStats)]
     _lib = L
     return L

@@ -65,8 +65,18 @@ enum {
   FM_C_ERR = 12,       // error bits (DtCtx::err points here in the CUDA library)
   FM_C_REQ = 13,       // sharded sweep: flip requests this rank found
   FM_C_BND = 14,       // sharded sweep: swept triangles with a vertex owned by another rank
-  FM_C_STAMP = 15      // next unused stamp
+  FM_C_STAMP = 15,     // next unused stamp
+  // [16..31]: state of a BATCH of warm Lloyd iterations queued without a host round trip
+  // (fm_iter_end, launch_kernels.cuh); the CUDA library allocates 32 ints
+  FM_T_HALT = 16,      // sticky: 0 run; FM_HALT_* = why the remaining launches of the batch do nothing
+  FM_T_ITERS = 17,     // iterations completed in the batch
+  FM_T_MAXDISP = 18,   // 64-bit: displacement word of the last completed iteration ([18], [19])
+  FM_T_FLIPS = 20,     // 64-bit: flips of the batch ([20], [21])
+  FM_T_SUB = 22,       // flip sub-rounds of the batch
+  FM_T_MAXQ = 23,      // largest flip queue of the batch
+  FM_T_TOL = 24        // double: convergence tolerance, written by the host when the batch starts ([24], [25])
 };
+enum { FM_HALT_CONVERGED = 1, FM_HALT_REBUILD = 2, FM_HALT_ERROR = 3 };
 
 // error bits reported through DtCtx::err
 enum { FM_E_WALK = 1, FM_E_TOPOLOGY = 2, FM_E_OVERFLOW = 4, FM_E_PEER = 8 };

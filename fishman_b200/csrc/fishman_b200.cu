@@ -11,6 +11,7 @@
 #include "../../include/fishman_b200.h"
 #include "launch_kernels.cuh"
 #include "mpas_kernels.cuh"
+#include "quality_kernels.cuh"
 
 using namespace fm;
 
@@ -83,6 +84,7 @@ struct fm_handle {
   int stamp = 1;  // host mirror (unused by the device-resident flip loop)
   int coop_blocks = 0, sms = 0;
   bool have_dt = false, have_cc = false, have_vd = false, have_edges = false;
+  bool dt_current = false;  // the connectivity is the Delaunay triangulation of the CURRENT generators
   // Voronoi
   P4* cc = nullptr;
   double *cclon = nullptr, *cclat = nullptr;
@@ -95,9 +97,10 @@ struct fm_handle {
     int *ring_edge = nullptr, *cells_on_vertex = nullptr, *edges_on_vertex = nullptr, *n_eoe = nullptr, *eoe = nullptr;
     double *xyz_edge = nullptr, *lonlat_edge = nullptr, *edge5 = nullptr;  // edge5: dv, dc, dv1, dv2, angle (5 x E)
     double *area_cell = nullptr, *area_tri = nullptr, *kite_ring = nullptr, *kite_vtx = nullptr, *weights = nullptr;
-    double* sums = nullptr;
+    double *sums = nullptr, *part = nullptr;
     bool have = false;
   } mp;
+  double* qbuf = nullptr;  // fm_quality: 16 histogram words, 6 extrema, 2 sums, then the block partials
   // peer exchange: `pts` and a PeerSync block live in one arena that is exported over CUDA IPC
   // and mapped by the other ranks of the mesh (fm_peer_handle / fm_peer_attach)
   char* arena = nullptr;
@@ -211,7 +214,7 @@ struct fm_handle {
     c.deg = deg; c.ring_tri = ring_tri; c.ring_nbr = ring_nbr;
     if (rho) c.rho = *rho;
     c.cell_begin = blk_begin; c.cell_end = blk_begin + blk_count;
-    c.maxdisp = (u64*)(counters + FM_C_MAXDISP); c.err = err;
+    c.maxdisp = (u64*)(counters + FM_C_MAXDISP); c.err = err; c.counters = counters;
     if (peers_attached)
       for (int k = 0; k < size; k++)
         if (k != rank) c.peer_pts[c.n_peers++] = (P4*)peer_base[k];
@@ -221,6 +224,7 @@ struct fm_handle {
 
 struct CudaBackend {
   fm_handle* h;
+  bool in_batch = false;  // inside a batch of warm iterations fm_iter_end has already cleared the counters
   template <class K>
   void launch(const DtCtx& c, int n) { h->launch<K, DtCtx>(c, n); }
   // K over [0, counters[idx]); `upper` bounds the count (threads past it leave after one load)
@@ -278,6 +282,7 @@ struct CudaBackend {
     // sources are tiny host constants; zero is the only value ever written
     bool allzero = true;
     for (int i = 0; i < n; i++) allzero = allzero && (src[i] == 0);
+    if (allzero && in_batch && dst == h->counters) return;
     if (allzero) h->note_cuda(cudaMemsetAsync(dst, 0, sizeof(int) * n, h->stream), "write_ints");
     else {
       h->note_cuda(cudaMemcpyAsync(dst, src, sizeof(int) * n, cudaMemcpyHostToDevice, h->stream), "write_ints");
@@ -407,11 +412,25 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
     return 1;
   }
   if (n < 4) { snprintf(g_create_err, sizeof g_create_err, "need at least 4 generators, got %d", n); return 1; }
+  if (n >= (1 << 28)) {  // adjacency words are (slot << 2 | edge) in an int32 and T = 2n - 4 slots must stay below 2^29
+    snprintf(g_create_err, sizeof g_create_err, "at most 2^28 - 1 generators (packed 32-bit adjacency), got %d", n);
+    return 1;
+  }
   if (size < 1 || rank < 0 || rank >= size) { snprintf(g_create_err, sizeof g_create_err, "bad rank/size"); return 1; }
   fm_handle* h = new fm_handle();
+  // staging of the set-up (keys, sort buffers): freed on every way out
+  u64 *k0 = nullptr, *k1 = nullptr;
+  int *i0 = nullptr, *dup = nullptr, *doff = nullptr;
+  auto free_staging = [&]() {
+    void* st[] = {k0, k1, i0, dup, doff};
+    for (void* q : st)
+      if (q) cudaFree(q);
+    k0 = k1 = nullptr; i0 = dup = doff = nullptr;
+  };
   auto bail = [&](const char* what, cudaError_t err) {
     snprintf(g_create_err, sizeof g_create_err, "fm_create: %s: %s", what,
              err == cudaSuccess ? h->errmsg : cudaGetErrorString(err));
+    free_staging();
     fm_destroy(h);
     return 1;
   };
@@ -432,7 +451,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   if (getenv("FM_NO_GRAPH")) h->graph_disabled = true;  // direct launches (profilers that do not follow graphs)
   A(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   A(cudaEventCreate(&h->ev0)); A(cudaEventCreate(&h->ev1));
-  A(cudaMallocHost((void**)&h->pinned, 64 * sizeof(int)));
+  A(cudaMallocHost((void**)&h->pinned, 96 * sizeof(int)));
   {  // arena = everything a peer rank touches (exported as ONE IPC allocation): generator records,
      // PeerSync block, flip-request inbox, circumcentres
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
@@ -449,6 +468,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
     h->inbox = (int*)(h->arena + h->off_inbox);
     h->cc = (P4*)(h->arena + h->off_cc);
     A(cudaMemsetAsync(h->psync, 0, sizeof(PeerSync), h->stream));
+    if (h->inbox_cap) A(cudaMemsetAsync(h->inbox, 0, sizeof(int) * (size_t)h->inbox_cap * size, h->stream));
     A(dalloc(&h->bnd, (size_t)h->inbox_cap));
   }
   A(dalloc(&h->orig, n)); A(dalloc(&h->inv, n)); A(dalloc(&h->v2t, n));
@@ -460,7 +480,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(dalloc(&h->rows, T));
   A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T)); A(dalloc(&h->fliplist, T / 2 + 1));
-  A(dalloc(&h->counters, 16));
+  A(dalloc(&h->counters, 32));
   h->err = h->counters + FM_C_ERR;
   A(dalloc(&h->winner, T)); A(dalloc(&h->vote, T)); A(dalloc(&h->mailbox, 3 * T)); A(dalloc(&h->scratch64, 4));
   A(cudaMemsetAsync(h->vote, 0xff, sizeof(u64) * T, h->stream));
@@ -468,14 +488,12 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
   A(cudaMemsetAsync(h->amark, 0, sizeof(int) * T, h->stream));
   A(cudaMemsetAsync(h->mailbox, 0, sizeof(u64) * 3 * T, h->stream));
   A(cudaMemsetAsync(h->pts, 0, sizeof(P4) * h->n_pad, h->stream));
-  int init_counters[16] = {0};
+  int init_counters[32] = {0};
   init_counters[FM_C_STAMP] = 1;  // first stamp
   A(cudaMemcpyAsync(h->counters, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, h->stream));
   A(cudaStreamSynchronize(h->stream));
   // staging: input order coordinates, keys, sort buffers
   double *ix = nullptr, *iy = nullptr, *iz = nullptr;
-  u64 *k0 = nullptr, *k1 = nullptr;
-  int *i0 = nullptr, *dup = nullptr;
   A(dalloc(&h->stage, 3 * (size_t)n));
   ix = h->stage; iy = ix + n; iz = iy + n;
   A(dalloc(&k0, n)); A(dalloc(&k1, n)); A(dalloc(&i0, n)); A(dalloc(&dup, 1));
@@ -518,23 +536,23 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
     h->lvl_K = K;
     h->lvl_off.assign(K + 2, 0);
     unsigned *lk = (unsigned*)k0, *lk2 = (unsigned*)k1;
-    int* doff = nullptr;
     A(dalloc(&doff, K + 2));
     fm_level_keys<<<nb, 256, 0, h->stream>>>(n, h->pts, K, lk, i0);
     bytes = h->cub_bytes;
-    A(cub::DeviceRadixSort::SortPairs(h->cub_tmp, bytes, lk, lk2, i0, h->lvl_order, n, 0, 4, h->stream));
+    int key_bits = 1;  // keys run 0..K (K = 12 with levels growing x4, up to 24 with x2)
+    while ((1 << key_bits) <= K + 1) key_bits++;
+    A(cub::DeviceRadixSort::SortPairs(h->cub_tmp, bytes, lk, lk2, i0, h->lvl_order, n, 0, key_bits, h->stream));
     fm_level_offsets<<<1, 32, 0, h->stream>>>(n, lk2, K, doff);
     A(cudaMemcpyAsync(h->lvl_off.data(), doff, sizeof(int) * (K + 2), cudaMemcpyDeviceToHost, h->stream));
     A(cudaStreamSynchronize(h->stream));
-    cudaFree(doff);
     h->n_launch += 3;
   }
-  cudaFree(k0); cudaFree(k1); cudaFree(i0); cudaFree(dup);
   if (hdup != big) {
     cudaMemcpy(&o1, h->orig + hdup, sizeof(int), cudaMemcpyDeviceToHost);
     snprintf(h->errmsg, sizeof h->errmsg, "DVT %d coincides with another DVT (duplicate generator)", o1 + 1);
     return bail("duplicate check", cudaSuccess);  // DV:286-288
   }
+  free_staging();
 #undef A
   *out = h;
   return 0;
@@ -559,7 +577,7 @@ extern "C" void fm_destroy(fm_handle* h) {
   {
     auto& m = h->mp;
     void* mptrs[] = {m.ring_edge, m.cells_on_vertex, m.edges_on_vertex, m.n_eoe, m.eoe, m.xyz_edge, m.lonlat_edge,
-                     m.edge5, m.area_cell, m.area_tri, m.kite_ring, m.kite_vtx, m.weights, m.sums};
+                     m.edge5, m.area_cell, m.area_tri, m.kite_ring, m.kite_vtx, m.weights, m.sums, m.part, h->qbuf};
     for (void* p : mptrs)
       if (p) cudaFree(p);
   }
@@ -584,13 +602,17 @@ extern "C" const char* fm_last_error(const fm_handle* h) { return h ? h->errmsg 
 // One readback for everything the host needs after a batch of launches: the eight counters,
 // the error bits and the displacement word.  Synchronises the stream.
 struct Readback {
-  int counters[16];
+  int counters[32];
   int err;
   int stamp;
   double maxdisp;
+  // state of a batch of warm iterations (FM_T_*)
+  int halt, iters, sub, maxq;
+  long long flips;
+  double batch_maxdisp;
 };
 static cudaError_t readback_enqueue(fm_handle* h) {
-  return cudaMemcpyAsync(h->pinned + 16, h->counters, 16 * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
+  return cudaMemcpyAsync(h->pinned + 16, h->counters, 32 * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
 }
 static int readback(fm_handle* h, Readback* r, const char* where, bool enqueued = false) {
   if (h->cuda_failed) return 1;
@@ -601,6 +623,11 @@ static int readback(fm_handle* h, Readback* r, const char* where, bool enqueued 
   r->err = r->counters[FM_C_ERR];
   r->stamp = r->counters[FM_C_STAMP];
   memcpy(&r->maxdisp, r->counters + FM_C_MAXDISP, sizeof(double));
+  r->halt = r->counters[FM_T_HALT]; r->iters = r->counters[FM_T_ITERS];
+  r->sub = r->counters[FM_T_SUB]; r->maxq = r->counters[FM_T_MAXQ];
+  memcpy(&r->flips, r->counters + FM_T_FLIPS, sizeof(long long));
+  memcpy(&r->batch_maxdisp, r->counters + FM_T_MAXDISP, sizeof(double));
+  if (r->halt) cudaMemsetAsync(h->counters + FM_T_HALT, 0, sizeof(int), h->stream);  // the batch is over
   if (r->err) {
     cudaMemsetAsync(h->err, 0, sizeof(int), h->stream);
     h->fail("%s: device reported error bits %d (%s%s%s%s)", where, r->err,
@@ -691,6 +718,7 @@ static int triangulate_cold(fm_handle* h) {
   account(h, r, st.rounds);
   h->n_cold++;
   h->have_dt = true; h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
+  h->dt_current = true;
   return 0;
 }
 
@@ -699,8 +727,9 @@ static void launch_peer_barrier(fm_handle* h, int phase);
 // sharded: (Lloyd loop on a mesh with attached peers) each rank sweeps its own triangle slots and
 // sends what it finds to all ranks; barrier; every rank applies all requests and runs the same
 // flip rounds.  Every rank must call this in step.
-static int repair_async(fm_handle* h, bool sharded = false) {
+static int repair_async(fm_handle* h, bool sharded = false, bool in_batch = false) {
   CudaBackend be{h};
+  be.in_batch = in_batch;
   DtCtx c = h->dt_ctx();
   c.cc = h->cc;
   DtStats st;
@@ -762,6 +791,7 @@ static int triangulate(fm_handle* h, bool warm, const char* where) {
       account(h, r, 0);
       h->n_warm++;
       h->have_cc = true; h->have_vd = false; h->have_edges = false; h->mp.have = false;
+      h->dt_current = true;
       return 0;
     }
   }
@@ -777,8 +807,17 @@ extern "C" int fm_counts(const fm_handle* h, int32_t* n_tri, int32_t* n_edge) {
   return 0;
 }
 
+// The generators moved since the connectivity was last brought to Delaunay (fm_lloyd ends with a
+// centroid update, fm_set_generators replaces them): repair it first, so that what leaves the
+// library is always the triangulation / diagram of the CURRENT generators.
+static int ensure_current(fm_handle* h, const char* where) {
+  if (h->have_dt && !h->dt_current) return triangulate(h, true, where);
+  return 0;
+}
+
 extern "C" int fm_get_triangles(fm_handle* h, int32_t* tri, int32_t* adj) {
   if (!h->have_dt) { h->fail("fm_get_triangles before fm_triangulate"); return 1; }
+  if (ensure_current(h, "fm_get_triangles")) return 1;
   int T = h->n_tri;
   int *dt = nullptr, *da = nullptr;
   FM_CUDA(dalloc(&dt, 3 * (size_t)T));
@@ -794,6 +833,7 @@ extern "C" int fm_get_triangles(fm_handle* h, int32_t* tri, int32_t* adj) {
 
 extern "C" int fm_voronoi(fm_handle* h, int32_t all) {
   if (!h->have_dt) { h->fail("voronoi_diagram before delaunay_triangulation"); return 1; }
+  if (ensure_current(h, "fm_voronoi")) return 1;
   size_t T = (size_t)h->n_tri;
   int n = h->n;
   if (circumcentres(h, true)) return 1;
@@ -882,6 +922,7 @@ extern "C" int fm_mpas(fm_handle* h, int32_t strict, int32_t* max_edges) {
     FM_CUDA(dalloc(&m.n_eoe, E)); FM_CUDA(dalloc(&m.xyz_edge, 3 * E)); FM_CUDA(dalloc(&m.lonlat_edge, 2 * E));
     FM_CUDA(dalloc(&m.edge5, 5 * E)); FM_CUDA(dalloc(&m.area_cell, n)); FM_CUDA(dalloc(&m.area_tri, T));
     FM_CUDA(dalloc(&m.kite_ring, 3 * T)); FM_CUDA(dalloc(&m.kite_vtx, 3 * T)); FM_CUDA(dalloc(&m.sums, 4));
+    FM_CUDA(dalloc(&m.part, 3 * ((T + 127) / 128)));
   }
   MpasCtx c;
   memset(&c, 0, sizeof c);
@@ -894,6 +935,7 @@ extern "C" int fm_mpas(fm_handle* h, int32_t strict, int32_t* max_edges) {
   c.area_cell = m.area_cell; c.area_tri = m.area_tri; c.kite_ring = m.kite_ring; c.kite_vtx = m.kite_vtx;
   c.cells_on_vertex = m.cells_on_vertex; c.edges_on_vertex = m.edges_on_vertex; c.n_eoe = m.n_eoe;
   c.sums = m.sums; c.maxdeg = h->counters + 7; c.err = h->err;
+  c.part = m.part; c.ps = (int)((T + 127) / 128);
   FM_CUDA(cudaMemsetAsync(m.sums, 0, 4 * sizeof(double), h->stream));
   FM_CUDA(cudaMemsetAsync(h->counters + 7, 0, sizeof(int), h->stream));
   const int B = 128;
@@ -902,6 +944,11 @@ extern "C" int fm_mpas(fm_handle* h, int32_t strict, int32_t* max_edges) {
   h->prof_begin(); fm_mpas_edges<<<nb(E), B, 0, h->stream>>>(c); h->prof_end("mpas_edges", E);
   h->prof_begin(); fm_mpas_cells<<<nb(n), B, 0, h->stream>>>(c); h->prof_end("mpas_cells", n);
   h->prof_begin(); fm_mpas_vertices<<<nb(T), B, 0, h->stream>>>(c); h->prof_end("mpas_vertices", T);
+  // the three sums of the reference's checks, in a fixed order (no floating-point atomics)
+  fm_sum_partials<<<1, 256, 0, h->stream>>>(m.part, (int)nb(n), 0, m.sums);
+  fm_sum_partials<<<1, 256, 0, h->stream>>>(m.part + 2 * c.ps, (int)nb(T), 0, m.sums + 1);
+  fm_sum_partials<<<1, 256, 0, h->stream>>>(m.part + c.ps, (int)nb(n), 0, m.sums + 2);
+  h->n_launch += 3;
   Readback r;
   if (readback(h, &r, "fm_mpas")) return 1;
   int me = r.counters[7];
@@ -987,7 +1034,7 @@ static void launch_peer_barrier(fm_handle* h, int phase) {
 }
 
 static Density make_density(const fm_density* rho);
-static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded);
+static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded, bool dry = false);
 // Centroid stage of one iteration.  On a sharded mesh with attached peers the kernel runs
 // between two barriers: no rank overwrites generators another rank is still reading, and the
 // iteration ends when every block has arrived everywhere.
@@ -997,11 +1044,15 @@ static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded) {
   if (h->peers_attached) launch_peer_barrier(h, 1);
 }
 
-static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded) {
+static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded, bool dry) {
   Density d = make_density(rho);
   VdCtx c = h->vd_ctx(&d);
   c.abort_flag = guarded ? h->counters + 3 : nullptr;
   int cnt = h->blk_count;
+  if (dry) {  // fm_quality: every cell, nothing moved, nothing sent
+    c.dry = 1; c.n_peers = 0; c.cell_begin = 0; c.cell_end = h->n; c.ringc = nullptr;
+    cnt = h->n;
+  }
   if (cnt <= 0) return;
   const int B = 128;
   size_t smem = sizeof(int) * kRingCap * B;
@@ -1020,11 +1071,20 @@ static bool same_density(const fm_density* a, const fm_density& b) {
          d.alpha == b.alpha && d.gamma == b.gamma;
 }
 
-// Queues one warm iteration (repair + centroid + readback copy) on the stream.  Outside
+static void launch_iter_end(fm_handle* h) {
+  h->prof_begin();
+  fm_iter_end<<<1, 1, 0, h->stream>>>(h->counters);
+  h->note_cuda(cudaGetLastError(), "iter_end");
+  h->prof_end("iter_end", 0);
+}
+
+// Queues one warm iteration (repair + centroid + fm_iter_end) on the stream; the host does not
+// look at anything in between (fm_iter_end takes the decisions, see lloyd_run).  Outside
 // profiling the sequence is captured once into a CUDA graph and replayed; every pointer and
 // size in it is fixed for the life of the handle, the stamp and the queue lengths live on the
 // device.  If capture is not possible the launches are issued directly.
 static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
+  const int launches = h->peers_attached ? 10 : 5;  // sweep, deferred sweep, flip loop, centroid, iter_end (+ fan-out, 3 barriers, apply)
   if (!h->profile && !h->graph_disabled) {
     if (h->warm_graph && !same_density(rho, h->warm_graph_rho)) {
       cudaGraphExecDestroy(h->warm_graph);
@@ -1036,11 +1096,11 @@ static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
       cudaError_t e = cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal);
       bool ok = (e == cudaSuccess);
       if (ok) {
-        int rc = repair_async(h, h->peers_attached);
+        int rc = repair_async(h, h->peers_attached, true);
         launch_centroid(h, rho, true);
-        cudaError_t e2 = readback_enqueue(h);
+        launch_iter_end(h);
         e = cudaStreamEndCapture(h->stream, &g);
-        ok = (rc == 0 && e2 == cudaSuccess && e == cudaSuccess && g != nullptr && !h->cuda_failed);
+        ok = (rc == 0 && e == cudaSuccess && g != nullptr && !h->cuda_failed);
       }
       if (ok) ok = cudaGraphInstantiate(&h->warm_graph, g, 0) == cudaSuccess;
       if (g) cudaGraphDestroy(g);
@@ -1059,47 +1119,98 @@ static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
       }
     }
     if (h->warm_graph) {
-      h->n_launch += h->peers_attached ? 9 : 4;  // sweep, deferred sweep, flip loop, centroid (+ fan-out, 3 barriers, apply)
+      h->n_launch += launches;
       cudaError_t e = cudaGraphLaunch(h->warm_graph, h->stream);
       if (e != cudaSuccess) { h->fail("cudaGraphLaunch: %s", cudaGetErrorString(e)); return 1; }
       return 0;
     }
   }
-  if (repair_async(h, h->peers_attached)) return 1;
+  if (repair_async(h, h->peers_attached, true)) return 1;
   launch_centroid(h, rho, true);
-  cudaError_t e = readback_enqueue(h);
-  if (e != cudaSuccess) { h->fail("readback: %s", cudaGetErrorString(e)); return 1; }
+  launch_iter_end(h);
   return 0;
 }
 
-// One Lloyd iteration on this rank's block.  Warm: sweep + cooperative flip loop + centroid
-// are queued back to back and the host waits once, for the displacement; if the sweep found
-// a turned-over triangle the device work was skipped and the iteration is redone cold.
-static int lloyd_iteration(fm_handle* h, const fm_density* rho, int warm, double* maxdisp) {
+// Starts a batch of warm iterations: per-iteration counters and the batch state cleared, the
+// tolerance where fm_iter_end reads it.  One small host -> device copy, no synchronisation.
+static int batch_begin(fm_handle* h, double tol) {
+  int* w = h->pinned + 64;  // 32 ints of pinned staging (the copy is asynchronous: the words must stay put)
+  memset(w, 0, 32 * sizeof(int));
+  memcpy(w + FM_T_TOL, &tol, sizeof(double));
+  // [0..14] and [16..31]; the stamp ([15]) lives on
+  FM_CUDA(cudaMemcpyAsync(h->counters, w, 15 * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+  FM_CUDA(cudaMemcpyAsync(h->counters + 16, w + 16, 16 * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+  return 0;
+}
+
+// One cold iteration: rebuild, circumcentres, centroid stage, readback.
+static int cold_iteration(fm_handle* h, const fm_density* rho, double* maxdisp) {
   Readback r;
-  if (warm && h->have_dt) {
-    if (warm_iteration_enqueue(h, rho)) return 1;
-    if (readback(h, &r, "fm_lloyd", true)) return 1;
-    if (r.counters[3] == 0) {
-      account(h, r, 0);
-      h->n_warm++;
-      h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
-      *maxdisp = r.maxdisp;
-      return 0;
-    }
-  }
   if (triangulate_cold(h)) return 1;
   if (circumcentres(h, false)) return 1;
   launch_centroid(h, rho, false);
   if (readback(h, &r, "fm_lloyd")) return 1;
   h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
+  h->dt_current = false;  // the generators moved after the triangulation
   *maxdisp = r.maxdisp;
   return h->cuda_failed ? 1 : 0;
 }
 
+// Up to max_iter Lloyd iterations on this rank's block, stopping when the displacement is <= tol.
+// Warm iterations (sweep + cooperative flip loop + centroid + fm_iter_end) are queued in batches
+// and the host waits ONCE per batch: the convergence test, the statistics and the decision "a
+// triangle turned over -> rebuild" are taken on the device by fm_iter_end after every iteration,
+// and the remaining launches of a batch that stopped early do nothing.  A turned-over triangle
+// stops the batch BEFORE its centroid stage; the host then redoes that iteration cold and goes on.
+static int lloyd_run(fm_handle* h, const fm_density* rho, int max_iter, double tol, int warm, int* iters,
+                     double* maxdisp) {
+  static const int kBatch = [] {
+    const char* e = getenv("FM_LLOYD_BATCH");
+    int v = e ? atoi(e) : 32;
+    return v >= 1 ? v : 1;
+  }();
+  int it = 0;
+  double md = 0.0;
+  while (it < max_iter) {
+    if (!(warm && h->have_dt)) {
+      if (cold_iteration(h, rho, &md)) return 1;
+      it++;
+      if (md <= tol) break;
+      continue;
+    }
+    int batch = max_iter - it < kBatch ? max_iter - it : kBatch;
+    if (batch_begin(h, tol)) return 1;
+    for (int b = 0; b < batch; b++)
+      if (warm_iteration_enqueue(h, rho)) return 1;
+    Readback r;
+    if (readback(h, &r, "fm_lloyd")) return 1;
+    h->tot_sub += r.sub; h->tot_flips += r.flips;
+    if (r.maxq > h->max_active) h->max_active = r.maxq;
+    h->n_warm += r.iters;
+    it += r.iters;
+    if (r.iters > 0) {
+      md = r.batch_maxdisp;
+      h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
+      h->dt_current = false;
+    }
+    if (r.halt == FM_HALT_CONVERGED) break;
+    if (r.halt == FM_HALT_REBUILD) {
+      if (cold_iteration(h, rho, &md)) return 1;
+      it++;
+      if (md <= tol) break;
+    } else if (r.halt == FM_HALT_ERROR || (r.halt == 0 && r.iters != batch)) {
+      h->fail("fm_lloyd: the device stopped a batch of iterations (halt %d after %d of %d)", r.halt, r.iters, batch);
+      return 1;
+    }
+  }
+  if (iters) *iters = it;
+  *maxdisp = md;
+  return 0;
+}
+
 extern "C" int fm_lloyd_local(fm_handle* h, const fm_density* rho, int32_t warm, double* max_disp) {
   double md = 0.0;
-  if (lloyd_iteration(h, rho, warm, &md)) return 1;
+  if (lloyd_run(h, rho, 1, -1.0, warm, nullptr, &md)) return 1;
   if (max_disp) *max_disp = md;
   return 0;
 }
@@ -1112,11 +1223,7 @@ extern "C" int fm_lloyd(fm_handle* h, const fm_density* rho, int32_t max_iter, d
   }
   double md = 0.0;
   int it = 0;
-  for (; it < max_iter;) {
-    if (lloyd_iteration(h, rho, warm, &md)) return 1;  // the convergence test needs the scalar on the host
-    it++;
-    if (md <= tol) break;
-  }
+  if (lloyd_run(h, rho, max_iter, tol, warm, &it, &md)) return 1;
   if (iters) *iters = it;
   if (max_disp) *max_disp = md;
   return 0;
@@ -1155,6 +1262,13 @@ extern "C" int fm_peer_attach(fm_handle* h, const void* handles) {
     }
   PeerCtx pc = {};
   pc.rank = h->rank; pc.size = h->size;
+  {  // how long a rank waits for a peer before it gives up with FM_E_PEER: ~2 s of SM clocks by default;
+     // raise it under profilers / kernel replay, or when a rank may be held up on the host
+    const char* e = getenv("FM_PEER_TIMEOUT_MS");
+    double ms = e ? atof(e) : 2000.0;
+    if (!(ms > 0.0)) ms = 2000.0;
+    pc.timeout_cycles = (long long)(ms * 2.0e6);  // ~2 GHz
+  }
   for (int k = 0; k < h->size; k++) {
     if (k == h->rank) { pc.sync[k] = h->psync; continue; }
     cudaIpcMemHandle_t hd;
@@ -1191,6 +1305,7 @@ static int xfer_generators(fm_handle* h, double* x, double* y, double* z, bool t
     FM_CUDA(cudaMemcpyAsync(iz, z, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     fm_gather_sorted<<<nb, 256, 0, h->stream>>>(n, h->orig, ix, iy, iz, h->pts, h->inv);
     h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
+    h->dt_current = false;
   }
   h->n_launch++;
   FM_CUDA(h->sync());
@@ -1202,6 +1317,100 @@ extern "C" int fm_get_generators(fm_handle* h, double* x, double* y, double* z) 
 }
 extern "C" int fm_set_generators(fm_handle* h, const double* x, const double* y, const double* z) {
   return xfer_generators(h, (double*)x, (double*)y, (double*)z, false);
+}
+
+// ---- one rank's block of generators (sharded handles): the host side of a rank holds, uploads and
+// downloads only the cells it owns
+extern "C" int fm_block_ids(fm_handle* h, int32_t* ids) {
+  int cnt = h->blk_count;
+  if (cnt <= 0) return 0;
+  int* d = (int*)h->stage;
+  fm_block_ids_kernel<<<(cnt + 255) / 256, 256, 0, h->stream>>>(cnt, h->pts + h->blk_begin, d);
+  h->n_launch++;
+  FM_CUDA(cudaMemcpyAsync(ids, d, sizeof(int) * cnt, cudaMemcpyDeviceToHost, h->stream));
+  FM_CUDA(h->sync());
+  return 0;
+}
+extern "C" int fm_get_generators_block(fm_handle* h, double* x, double* y, double* z) {
+  int cnt = h->blk_count;
+  if (cnt <= 0) return 0;
+  double *ix = h->stage, *iy = ix + cnt, *iz = iy + cnt;
+  fm_block_unpack<<<(cnt + 255) / 256, 256, 0, h->stream>>>(cnt, h->pts + h->blk_begin, ix, iy, iz);
+  h->n_launch++;
+  FM_CUDA(cudaMemcpyAsync(x, ix, sizeof(double) * cnt, cudaMemcpyDeviceToHost, h->stream));
+  FM_CUDA(cudaMemcpyAsync(y, iy, sizeof(double) * cnt, cudaMemcpyDeviceToHost, h->stream));
+  FM_CUDA(cudaMemcpyAsync(z, iz, sizeof(double) * cnt, cudaMemcpyDeviceToHost, h->stream));
+  FM_CUDA(h->sync());
+  return 0;
+}
+extern "C" int fm_set_generators_block(fm_handle* h, const double* x, const double* y, const double* z) {
+  if (h->size > 1 && !h->peers_attached) {
+    h->fail("fm_set_generators_block on a sharded handle needs fm_peer_attach (the block is stored into every rank's array)");
+    return 1;
+  }
+  int cnt = h->blk_count;
+  double *ix = h->stage, *iy = ix + cnt, *iz = iy + cnt;
+  if (cnt > 0) {
+    FM_CUDA(cudaMemcpyAsync(ix, x, sizeof(double) * cnt, cudaMemcpyHostToDevice, h->stream));
+    FM_CUDA(cudaMemcpyAsync(iy, y, sizeof(double) * cnt, cudaMemcpyHostToDevice, h->stream));
+    FM_CUDA(cudaMemcpyAsync(iz, z, sizeof(double) * cnt, cudaMemcpyHostToDevice, h->stream));
+    BlockFan f = {};
+    f.n_dst = 0;
+    f.dst[f.n_dst++] = h->pts + h->blk_begin;
+    if (h->peers_attached)
+      for (int k = 0; k < h->size; k++)
+        if (k != h->rank) f.dst[f.n_dst++] = (P4*)h->peer_base[k] + h->blk_begin;
+    h->prof_begin();
+    fm_block_pack_fan<<<(cnt + 255) / 256, 256, 0, h->stream>>>(cnt, ix, iy, iz, f);
+    h->note_cuda(cudaGetLastError(), "block_fanout");
+    h->prof_end("block_fanout", cnt);
+  }
+  if (h->peers_attached) launch_peer_barrier(h, 3);  // every rank's block has landed everywhere
+  h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
+  h->dt_current = false;
+  FM_CUDA(h->sync());
+  return 0;
+}
+
+// ---- mesh-quality statistics (quality_kernels.cuh)
+extern "C" int fm_quality(fm_handle* h, const fm_density* rho, fm_quality_stats* out) {
+  if (!h->have_dt) { h->fail("fm_quality before fm_triangulate"); return 1; }
+  if (ensure_current(h, "fm_quality")) return 1;
+  if (!h->have_cc && circumcentres(h, false)) return 1;
+  const int B = 128;
+  int n = h->n, T = h->n_tri;
+  int nbc = (n + B - 1) / B, nbt = (T + B - 1) / B;
+  size_t words = 16 + 6 + 2 + 2 * (size_t)nbt;
+  if (!h->qbuf) FM_CUDA(dalloc(&h->qbuf, words));
+  double init[24];
+  memset(init, 0, sizeof init);
+  const double big = 1.0e300;
+  init[16] = big; init[18] = big; init[20] = big;   // minima
+  FM_CUDA(cudaMemcpyAsync(h->qbuf, init, sizeof init, cudaMemcpyHostToDevice, h->stream));
+  QualityCtx q;
+  memset(&q, 0, sizeof q);
+  q.vd = h->vd_ctx(nullptr);
+  q.hist = (unsigned long long*)h->qbuf; q.mm = h->qbuf + 16; q.part = h->qbuf + 24; q.stride = nbt;
+  h->prof_begin(); fm_quality_cells<<<nbc, B, 0, h->stream>>>(q); h->prof_end("quality_cells", n);
+  h->prof_begin(); fm_quality_triangles<<<nbt, B, 0, h->stream>>>(q); h->prof_end("quality_triangles", T);
+  fm_sum_partials<<<1, 256, 0, h->stream>>>(q.part, nbc, 0, h->qbuf + 22);
+  fm_sum_partials<<<1, 256, 0, h->stream>>>(q.part + nbt, nbt, 0, h->qbuf + 23);
+  h->n_launch += 2;
+  // the largest generator-to-centroid chord: the Lloyd kernel over ALL cells, moving nothing
+  FM_CUDA(cudaMemsetAsync(h->counters + FM_C_MAXDISP, 0, sizeof(u64), h->stream));
+  launch_centroid_kernel(h, rho, false, true);
+  double host[24];
+  FM_CUDA(cudaMemcpyAsync(host, h->qbuf, sizeof host, cudaMemcpyDeviceToHost, h->stream));
+  Readback r;
+  if (readback(h, &r, "fm_quality")) return 1;
+  FM_CUDA(cudaMemsetAsync(h->counters + FM_C_MAXDISP, 0, sizeof(u64), h->stream));
+  memcpy(out->degree_hist, host, 16 * sizeof(int64_t));
+  out->area_cell_min = host[16]; out->area_cell_max = host[17];
+  out->area_tri_min = host[18]; out->area_tri_max = host[19];
+  out->angle_min = host[20]; out->angle_max = host[21];
+  out->area_cell_sum = host[22]; out->area_tri_sum = host[23];
+  out->max_disp = r.maxdisp;
+  return 0;
 }
 
 static Density make_density(const fm_density* rho) {

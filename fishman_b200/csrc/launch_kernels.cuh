@@ -16,6 +16,17 @@ __device__ __forceinline__ void use_device_stamp(DtCtx& c) {
 }
 __device__ __forceinline__ void use_device_stamp(VdCtx&) {}
 
+// A batch of warm Lloyd iterations is queued without the host looking in between
+// (fm_iter_end below).  Once an iteration of the batch converged, found a turned-over triangle
+// or hit an error, every later launch of the batch leaves at once; the same after a peer rank
+// missed a barrier (FM_E_PEER): the data of that iteration never arrived.
+__device__ __forceinline__ bool fm_halted(const int* counters) {
+  return counters && ((((volatile const int*)counters)[FM_T_HALT] != 0) ||
+                      ((((volatile const int*)counters)[FM_C_ERR] & FM_E_PEER) != 0));
+}
+__device__ __forceinline__ bool fm_halted(const DtCtx& c) { return fm_halted(c.counters); }
+__device__ __forceinline__ bool fm_halted(const VdCtx& c) { return fm_halted(c.counters); }
+
 // Resident 256-thread blocks per SM the launcher asks ptxas to make room for.  The gather
 // kernels are latency / L1 bound; their filter-only forms (K<false>) contain no calls and
 // fit 64 registers without spilling, so four blocks hide the gather latency.
@@ -29,12 +40,14 @@ template <> struct KOcc<KCheckT<false>> { static const int value = 4; };
 template <class K, class Ctx>
 __global__ void __launch_bounds__(256, KOcc<K>::value) fm_kernel(Ctx c, int n) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (fm_halted(c)) return;
   use_device_stamp(c);
   if (i < n) K::run(c, i);
 }
 // K over [0, counters[idx]): the count lives on the device, the host launches for an upper bound
 template <class K>
 __global__ void __launch_bounds__(256) fm_kernel_counted(DtCtx c, int idx) {
+  if (fm_halted(c)) return;
   use_device_stamp(c);
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < c.counters[idx]) K::run(c, i);
@@ -44,6 +57,7 @@ __global__ void __launch_bounds__(256) fm_kernel_counted(DtCtx c, int idx) {
 // the count is only known on the device).
 template <class K>
 __global__ void __launch_bounds__(128) fm_kernel_deferred(DtCtx c) {
+  if (fm_halted(c)) return;
   use_device_stamp(c);
   int m = c.counters[FM_C_SLOW];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) K::run(c, c.slow[i]);
@@ -65,6 +79,7 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
   int* list[2] = {listA, listB};
   volatile int* vc = c.counters;
   int stamp = vc[FM_C_STAMP];
+  if (fm_halted(c)) return;
   if (vc[3] > 0) return;  // a triangle turned over: leave everything to the rebuild
   int sub = 0, maxq = 0;
   for (;; sub++) {
@@ -105,6 +120,25 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
 
 __global__ void fm_bump_stamp(int* counters, int by) { counters[FM_C_STAMP] += by; }
 
+// Last launch of a warm Lloyd iteration: what the host used to do after reading the counters
+// back -- the convergence test (north-star kernel (d): the displacement maximum is already
+// reduced), the "a triangle turned over, rebuild" decision, the statistics -- and the reset of
+// the per-iteration counters for the next iteration of the batch.
+__global__ void fm_iter_end(int* counters) {
+  if (counters[FM_T_HALT]) return;
+  if (counters[FM_C_ERR]) { counters[FM_T_HALT] = FM_HALT_ERROR; return; }   // counters kept for the report
+  if (counters[3] > 0) { counters[FM_T_HALT] = FM_HALT_REBUILD; return; }    // the centroid kernel did nothing
+  const u64 md = *(const u64*)(counters + FM_C_MAXDISP);
+  *(u64*)(counters + FM_T_MAXDISP) = md;
+  counters[FM_T_ITERS] += 1;
+  *(u64*)(counters + FM_T_FLIPS) += (u64)counters[2];
+  counters[FM_T_SUB] += counters[5];
+  if (counters[6] > counters[FM_T_MAXQ]) counters[FM_T_MAXQ] = counters[6];
+  if (__longlong_as_double((long long)md) <= *(const double*)(counters + FM_T_TOL)) counters[FM_T_HALT] = FM_HALT_CONVERGED;
+#pragma unroll
+  for (int k = 0; k < 15; k++) counters[k] = 0;
+}
+
 // bookkeeping at the end of a host-driven flip sub-round (what thread 0 of fm_flip_coop does)
 __global__ void fm_subround_end(int* counters, int cur, int nact) {
   counters[cur] = 0;
@@ -127,6 +161,7 @@ __global__ void fm_subround_end(int* counters, int cur, int nact) {
 template <bool UNIFORM>
 __global__ void __launch_bounds__(128, UNIFORM ? FM_OCC_CENTROID : FM_OCC_CENTROID_RHO) fm_centroid_update(const VdCtx c, int n) {
   extern __shared__ int ring_smem[];
+  if (fm_halted(c)) return;
   if (c.abort_flag && *c.abort_flag) return;
   int j = blockIdx.x * blockDim.x + threadIdx.x;
   double disp = 0.0;
@@ -161,6 +196,7 @@ struct PeerSync {
 struct PeerCtx {
   PeerSync* sync[8];  // by rank; sync[rank] is the local block
   int rank, size;
+  long long timeout_cycles;  // SM clocks a rank waits for a peer before it sets FM_E_PEER (FM_PEER_TIMEOUT_MS)
 };
 // phase 0 (before the centroid kernel: every rank has finished reading the generators),
 // phase 1 (after it: every rank's stores into this rank's generator array have landed, and the
@@ -171,6 +207,7 @@ struct PeerCtx {
 __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
   __shared__ int ep;
   const int k = threadIdx.x;
+  if (fm_halted(counters)) return;  // every rank takes the same decision (combined counts / maxima), or it is an error path
   PeerSync* self = pc.sync[pc.rank];
   if (k == 0) {
     ep = self->epoch + 1;
@@ -192,7 +229,7 @@ __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
     *(volatile int*)&pc.sync[k]->flag[pc.rank] = e;
     long long t0 = clock64();
     while (*(volatile int*)&self->flag[k] < e) {
-      if (clock64() - t0 > 4000000000LL) { atomicOr(counters + FM_C_ERR, FM_E_PEER); break; }
+      if (clock64() - t0 > pc.timeout_cycles) { atomicOr(counters + FM_C_ERR, FM_E_PEER); break; }
     }
   }
   __syncthreads();
@@ -228,6 +265,7 @@ struct FanCtx {
   int rank, size, blk_per;
 };
 __global__ void __launch_bounds__(256) fm_sweep_fanout(FanCtx f) {
+  if (fm_halted(f.counters)) return;
   const int gsz = gridDim.x * blockDim.x, gid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nreq = f.counters[FM_C_REQ], nbnd = f.counters[FM_C_BND];
   for (int i = gid; i < nreq; i += gsz) {
@@ -251,6 +289,7 @@ __global__ void __launch_bounds__(256) fm_sweep_fanout(FanCtx f) {
 // entry -- and adds up the turned-over counts.  Votes are atomicMin and the flip rounds depend
 // only on the SET of queued triangles, so every rank goes on to the same flips.
 __global__ void __launch_bounds__(256) fm_apply_requests(DtCtx c, PeerCtx pc, const int* inbox, int cap) {
+  if (fm_halted(c)) return;
   use_device_stamp(c);
   const PeerSync* self = pc.sync[pc.rank];
   const int gsz = gridDim.x * blockDim.x, gid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -373,6 +412,28 @@ __global__ void fm_scatter_orig(int n, const P4* pts, double* x, double* y, doub
     int o = (int)q.id;
     x[o] = q.x; y[o] = q.y; z[o] = q.z;
   }
+}
+
+// ---- one rank's block of generators in block order (fm_block_ids / fm_get_generators_block /
+// fm_set_generators_block)
+__global__ void fm_block_ids_kernel(int cnt, const P4* blk, int* ids) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < cnt) ids[i] = (int)blk[i].id + 1;
+}
+__global__ void fm_block_unpack(int cnt, const P4* blk, double* x, double* y, double* z) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < cnt) { P4 q = blk[i]; x[i] = q.x; y[i] = q.y; z[i] = q.z; }
+}
+struct BlockFan {
+  P4* dst[8];   // this rank's block inside every rank's generator array ([0] = the local one)
+  int n_dst;
+};
+__global__ void fm_block_pack_fan(int cnt, const double* x, const double* y, const double* z, BlockFan f) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cnt) return;
+  P4 q = f.dst[0][i];           // keeps the id
+  q.x = x[i]; q.y = y[i]; q.z = z[i];
+  for (int k = 0; k < f.n_dst; k++) f.dst[k][i] = q;
 }
 
 // duplicates share a Morton key, so they sit in one run of equal keys

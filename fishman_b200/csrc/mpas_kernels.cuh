@@ -36,6 +36,8 @@ struct MpasCtx {
   int* eoe;            // 2 max_edges x E
   double* weights;     // 2 max_edges x E
   double* sums;        // [0] cells, [1] triangles, [2] kites, [3] max |sum R - 1|
+  double* part;        // block partials of the three sums: cells at [0, ps), kites at [ps, 2 ps), triangles at [2 ps, 3 ps)
+  int ps;
   int* maxdeg;
   int* err;
 };
@@ -128,10 +130,31 @@ __global__ void fm_mpas_edges(MpasCtx c) {
   c.angle[e] = m_angle(m_lonlat_xyz(xlon, asin(A.z)), A, B);
 }
 
-__device__ __forceinline__ void m_block_add(double v, double* dst) {
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  if ((threadIdx.x & 31) == 0 && v != 0.0) atomicAdd(dst, v);
+// Deterministic sums (the reference's Sum = 4 pi +- 1e-10 verdicts must not depend on the order
+// in which atomics happen to land): no floating-point atomics.
+// Sum of v over the block, returned to thread 0 (same value on every run: the shape of the tree
+// depends on blockDim only).  smem: one double per warp.
+__device__ __forceinline__ double fm_block_sum(double v, double* smem) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();  // smem may still be read from a previous call
+  if ((threadIdx.x & 31) == 0) smem[w] = v;
+  __syncthreads();
+  double s = 0.0;
+  if (threadIdx.x == 0)
+    for (int k = 0; k < nw; k++) s += smem[k];
+  return s;
 }
+// out[q] = sum of part[q * stride + 0 .. nb), q = blockIdx.x: fixed order, one block per quantity
+__global__ void __launch_bounds__(256) fm_sum_partials(const double* part, int nb, int stride, double* out) {
+  __shared__ double smem[8];
+  const double* p = part + (size_t)blockIdx.x * stride;
+  double v = 0.0;
+  for (int i = threadIdx.x; i < nb; i += blockDim.x) v += p[i];
+  double s = fm_block_sum(v, smem);
+  if (threadIdx.x == 0) out[blockIdx.x] = s;
+}
+
 
 // per cell: areaCell (MM:296-308) and its kites in ring order (MM:324-341):
 // kite(j) = area(xEdge(edge j), cell, xEdge(edge j-1), vertex j)
@@ -158,8 +181,9 @@ __global__ void fm_mpas_cells(MpasCtx c) {
     double dev = fabs(ksum / area - 1.0);                           // sum of R over the cell, MM:469-475
     atomicMax((unsigned long long*)(c.sums + 3), (unsigned long long)__double_as_longlong(dev));
   }
-  m_block_add(area, c.sums);
-  m_block_add(ksum, c.sums + 2);
+  __shared__ double smem[4];
+  double sa = fm_block_sum(area, smem), sk = fm_block_sum(ksum, smem);
+  if (threadIdx.x == 0) { c.part[blockIdx.x] = sa; c.part[c.ps + blockIdx.x] = sk; }
 }
 
 // per Voronoi vertex (= triangle slot): cellsOnVertex / edgesOnVertex in the reference's final
@@ -176,7 +200,7 @@ __global__ void fm_mpas_vertices(MpasCtx c) {
       int cell = (int)q[k].id, b = c.off[cell], d = c.off[cell + 1] - b, pos = -1;
       for (int j = 0; j < d; j++)
         if (c.ring_tri[b + j] == t + 1) { pos = b + j; break; }
-      if (pos < 0) { atomicOr(c.err, FM_E_TOPOLOGY); return; }
+      if (pos < 0) { atomicOr(c.err, FM_E_TOPOLOGY); pos = b; }  // reported; the block still reaches its barrier
       ed[k] = c.ring_edge[pos];   // edge (v[k], v[k-1]): the first of the two edges at v[k], counter-clockwise
       kite[k] = c.kite_ring[pos];
     }
@@ -192,7 +216,9 @@ __global__ void fm_mpas_vertices(MpasCtx c) {
     area = m_angle(cc, a, b) + m_angle(a, b, cc) + m_angle(b, cc, a) - kPi;
     c.area_tri[t] = area;
   }
-  m_block_add(area, c.sums + 1);
+  __shared__ double smem[4];
+  double sa = fm_block_sum(area, smem);
+  if (threadIdx.x == 0) c.part[2 * c.ps + blockIdx.x] = sa;
 }
 
 // per edge: edgesOnEdge (MM:271-294) and weightsOnEdge (calc_weightsOnEdge, MM:505-556).

@@ -50,6 +50,8 @@ struct VdCtx {
   int cell_begin, cell_end;   // range of internal cells this rank updates
   u64* maxdisp;               // bits of the largest chord displacement (>= 0, so ordered)
   const int* abort_flag;      // when non-null and != 0 the Lloyd kernel does nothing
+  const int* counters;        // CUDA library: the handle's counter block (halt word of a batch), or null
+  int dry;                    // != 0: compute the displacements only, move nothing (fm_quality)
   int* err;
   // peer exchange (fm_peer_attach): the generator arrays of the other ranks, mapped into this
   // process over NVLink; the Lloyd kernel stores every updated generator there as well, so the
@@ -430,9 +432,11 @@ struct KCentroid {
     if (!(nrm > 0.0)) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
     double n0 = M0 / nrm, n1 = M1 / nrm, n2 = M2 / nrm;
     double dx = n0 - g.x, dy = n1 - g.y, dz = n2 - g.z;
-    const P4 moved{n0, n1, n2, gq.id};  // whole 32-byte records: one store, one full sector / NVLink packet
-    c.pts[i] = moved;
-    for (int q = 0; q < c.n_peers; q++) c.peer_pts[q][i] = moved;
+    if (!c.dry) {
+      const P4 moved{n0, n1, n2, gq.id};  // whole 32-byte records: one store, one full sector / NVLink packet
+      c.pts[i] = moved;
+      for (int q = 0; q < c.n_peers; q++) c.peer_pts[q][i] = moved;
+    }
     return sqrt(dx * dx + dy * dy + dz * dz);
   }
   FM_HD static void run(const VdCtx& c, int j) {  // generic form (host tests)

@@ -220,6 +220,33 @@ class Mesh:
     def get_generators_soa(self, x, y, z):
         self._chk(_lib.lib().fm_get_generators(self._h, _d(x), _d(y), _d(z)))
 
+    # ---- one rank's block (sharded meshes): the host side holds only the cells the rank owns
+    def block_count(self):
+        """cells of this rank's block that exist (the last rank's block may be padded)"""
+        _, _, beg, cnt = self.generator_block()
+        return int(max(0, min(cnt, self.n - beg)))
+
+    def block_ids(self):
+        """1-based input-order ids of the block's cells, in block order"""
+        ids = np.empty(self.block_count(), dtype=np.int32)
+        self._chk(_lib.lib().fm_block_ids(self._h, _i(ids)))
+        return ids
+
+    def get_generators_block_soa(self, x, y, z):
+        self._chk(_lib.lib().fm_get_generators_block(self._h, _d(x), _d(y), _d(z)))
+
+    def set_generators_block_soa(self, x, y, z):
+        """Upload this rank's block (block order); it is stored into every rank's array over NVLink.
+        Every rank of the mesh must call it in step."""
+        self._chk(_lib.lib().fm_set_generators_block(self._h, _d(x), _d(y), _d(z)))
+
+    def quality(self, rho=None):
+        """Mesh-quality statistics of the current generators (fm_quality): dict."""
+        rho = rho or density_uniform()
+        q = _lib.QualityStats()
+        self._chk(_lib.lib().fm_quality(self._h, C.byref(rho), C.byref(q)))
+        return q.asdict()
+
     # ---- Lloyd (SURVEY.md 7.3)
     def lloyd(self, rho=None, max_iter=1, tol=0.0, warm=True):
         rho = rho or density_uniform()

@@ -145,8 +145,38 @@ int fm_peer_handle(fm_handle* h, void* out80);
 int fm_peer_attach(fm_handle* h, const void* handles);
 /* generators in input order (device -> host) */
 int fm_get_generators(fm_handle* h, double* x, double* y, double* z);
-/* replace the generators (host -> device), keeping the internal order and topology */
+/* replace the generators (host -> device), keeping the internal order and topology.
+ * Contract: after fm_set_generators or fm_lloyd (which ends with a centroid update) the stored
+ * connectivity is that of the PREVIOUS generators; fm_get_triangles, fm_voronoi and fm_quality
+ * repair it first (as fm_retriangulate(h, 1)), so what they return always belongs to the current
+ * generators. */
 int fm_set_generators(fm_handle* h, const double* x, const double* y, const double* z);
+
+/* One rank's block (fm_create_dist): the host side of rank r holds only the cells it owns.
+ * fm_block_ids: the 1-based input-order ids of the block's cells, in block order (count entries,
+ * fm_generator_block gives the count; the last rank's block may be shorter: only ids <= N count).
+ * fm_get_generators_block / fm_set_generators_block move 3 x count doubles in that order; the
+ * upload is stored into EVERY rank's generator array over NVLink (the same record stores the
+ * Lloyd kernel uses) and ends with a device-side barrier, so all ranks must call it in step.
+ * On an unsharded handle the block is the whole set in internal (space-filling-curve) order. */
+int fm_block_ids(fm_handle* h, int32_t* ids);
+int fm_get_generators_block(fm_handle* h, double* x, double* y, double* z);
+int fm_set_generators_block(fm_handle* h, const double* x, const double* y, const double* z);
+
+/* Mesh-quality statistics of the CURRENT generators: cell-degree histogram
+ * (degree d in bin d, d >= 15 in bin 15), Voronoi cell and Delaunay triangle areas by the
+ * reference's angle-excess formula (calc_area SG:198-227 over calc_sphere_angle SG:247-285; the sums
+ * are its checks MM:306 / MM:320 against 4 pi), smallest / largest interior angle of the Delaunay
+ * triangles (radians), and the largest chord between a generator and the centroid of its cell under
+ * rho (the displacement the next Lloyd step would make; nothing is moved).  Sums are deterministic. */
+typedef struct fm_quality_stats {
+  int64_t degree_hist[16];
+  double area_cell_min, area_cell_max, area_cell_sum;
+  double area_tri_min, area_tri_max, area_tri_sum;
+  double angle_min, angle_max;
+  double max_disp;
+} fm_quality_stats;
+int fm_quality(fm_handle* h, const fm_density* rho, fm_quality_stats* out);
 
 /* Page-locked host buffers for the arrays that cross the boundary (optional: any host
  * pointer is accepted, pinned ones copy at full PCIe rate). */

@@ -1079,6 +1079,58 @@ int fo_areas(fo_mesh *m, double *area_cell, double *area_tri, double *sum_cell, 
   return 0;
 }
 
+/* Mesh-quality statistics (last sentence; no reference procedure of its own: the
+   building blocks are calc_area SG:198-227, calc_sphere_angle SG:247-285, the Sum = 4 pi checks
+   MM:306 / MM:320, and the centroid map of fo_centroids).  Layout = fm_quality_stats. */
+typedef struct fo_quality_stats {
+  long long degree_hist[16];
+  double area_cell_min, area_cell_max, area_cell_sum;
+  double area_tri_min, area_tri_max, area_tri_sum;
+  double angle_min, angle_max;
+  double max_disp;
+} fo_quality_stats;
+
+int fo_quality(fo_mesh *m, const fo_density *rho, fo_quality_stats *q) {
+  int n = m->n, i, t, k;
+  double *ac, *at, *g;
+  if (!m->have_vd) return fo_fail(m, "quality before voronoi_diagram");
+  memset(q, 0, sizeof *q);
+  ac = (double *)malloc(sizeof(double) * n);
+  at = (double *)malloc(sizeof(double) * m->nT);
+  if (fo_areas(m, ac, at, &q->area_cell_sum, &q->area_tri_sum)) { free(ac); free(at); return 1; }
+  q->area_cell_min = q->area_tri_min = q->angle_min = 1e300;
+  for (i = 0; i < n; i++) {
+    int d = m->ring_off[i + 1] - m->ring_off[i];
+    q->degree_hist[d < 15 ? d : 15]++;
+    if (ac[i] < q->area_cell_min) q->area_cell_min = ac[i];
+    if (ac[i] > q->area_cell_max) q->area_cell_max = ac[i];
+  }
+  for (t = 0; t < m->nT; t++) {
+    double p[3][3];
+    if (at[t] < q->area_tri_min) q->area_tri_min = at[t];
+    if (at[t] > q->area_tri_max) q->area_tri_max = at[t];
+    for (k = 0; k < 3; k++) {
+      int v = m->tri[3 * t + k];
+      p[k][0] = m->x[v]; p[k][1] = m->y[v]; p[k][2] = m->z[v];
+    }
+    for (k = 0; k < 3; k++) {
+      double a = calc_sphere_angle(p[(k + 2) % 3], p[k], p[(k + 1) % 3]);
+      if (a < q->angle_min) q->angle_min = a;
+      if (a > q->angle_max) q->angle_max = a;
+    }
+  }
+  free(ac); free(at);
+  g = (double *)malloc(sizeof(double) * 3 * n);
+  if (fo_centroids(m, rho, g, g + n, g + 2 * n)) { free(g); return 1; }
+  for (i = 0; i < n; i++) {
+    double dx = g[i] - m->x[i], dy = g[n + i] - m->y[i], dz = g[2 * n + i] - m->z[i];
+    double dd = sqrt(dx * dx + dy * dy + dz * dz);
+    if (dd > q->max_disp) q->max_disp = dd;
+  }
+  free(g);
+  return 0;
+}
+
 /* ------------------------------------------- MPAS adapter arithmetic (MM) */
 /* Restates mpas_mesh_adapt (MM:181-345) and calc_weightsOnEdge (MM:442-561) on
    flat arrays, with the container graph the reference walks rebuilt first:

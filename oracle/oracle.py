@@ -32,6 +32,17 @@ class Stats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class QualityStats(C.Structure):
+    _fields_ = [("degree_hist", C.c_longlong * 16)] + [(k, C.c_double) for k in (
+        "area_cell_min", "area_cell_max", "area_cell_sum", "area_tri_min", "area_tri_max", "area_tri_sum",
+        "angle_min", "angle_max", "max_disp")]
+
+    def asdict(self):
+        d = {k: getattr(self, k) for k, _ in self._fields_[1:]}
+        d["degree_hist"] = [int(v) for v in self.degree_hist]
+        return d
+
+
 class Density(C.Structure):
     _fields_ = [("kind", C.c_int), ("cx", C.c_double), ("cy", C.c_double), ("cz", C.c_double),
                 ("beta", C.c_double), ("alpha", C.c_double), ("gamma", C.c_double)]
@@ -88,6 +99,7 @@ def lib():
         L.fo_calc_area.restype = C.c_double
         L.fo_calc_area.argtypes = [C.c_int, dp, dp, dp]
         L.fo_areas.argtypes = [vp, dp, dp, dp, dp]
+        L.fo_quality.argtypes = [vp, C.POINTER(Density), C.POINTER(QualityStats)]
         L.fo_mpas.argtypes = [vp, C.c_int, ip]
         L.fo_mpas_get_edges.argtypes = [vp, ip, ip, dp, dp, dp, dp, dp, dp, dp]
         L.fo_mpas_get_cells.argtypes = [vp, ip, ip, ip, ip, dp]
@@ -195,6 +207,12 @@ class Oracle:
         self._chk(lib().fo_areas(self._h, _d(ac), _d(at), C.byref(sc), C.byref(st)))
         return ac, at, sc.value, st.value
 
+
+    def quality(self, rho=None):
+        """Mesh-quality statistics (fo_quality) of the current triangulation + Voronoi diagram: dict."""
+        q = QualityStats()
+        self._chk(lib().fo_quality(self._h, C.byref(rho or density_uniform()), C.byref(q)))
+        return q.asdict()
 
     def mpas(self, strict=True):
         """mpas_mesh_adapt + calc_weightsOnEdge (src/mpas_mesh_mod.F90:181-345, :442-561) as a dict

@@ -122,11 +122,26 @@ def test_c2_ico7_lloyd_steps_against_oracle():
     m = fb.Mesh.from_xyz(p)
     o = O.Oracle(p)
     rho_g, rho_o = fb.density_uniform(), O.density_uniform()
+    # The reference draws its first three vertices at random (DV:595-610) and builds VIRTUAL antipodes
+    # of them (DV:630-639).  ICO(k) is antipodally symmetric, so an antipode lands within the
+    # reference's 1e-4 coincidence window of a real generator (DV:1972-1983) and, once Lloyd has moved
+    # the points a little, the reference's own fatal checks can fire ("coincides with vertex",
+    # "Failed to update DVT ... after delete DT", DV:286/310) for some triples and not for others.
+    # A fatal triple is a stop 1 of the reference; like a re-run of it, take the next triple.
+    triples = [(0, 1, 2), (3, 30011, 90001), (100, 2000, 30000), (7, 77777, 150000), (12345, 54321, 99999)]
     for it in range(5):
         g0 = m.generators()
         n_it, md = m.lloyd(rho_g, max_iter=1, warm=True)
-        o.set_generators(g0)
-        omd = o.lloyd_step(rho_o)          # DT + VD of g0, then the centroid update
+        omd = None
+        for f3 in triples:
+            o.first3 = f3
+            o.set_generators(g0)
+            try:
+                omd = o.lloyd_step(rho_o)          # DT + VD of g0, then the centroid update
+                break
+            except O.OracleError as e:
+                print("C2 step", it, "reference restatement stops with", f3, ":", e)
+        assert omd is not None
         og, g1 = o.generators(), m.generators()
         assert np.abs(g1 - og).max() < 1e-12, it
         assert abs(md - omd) < 1e-12, it

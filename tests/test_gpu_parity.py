@@ -253,3 +253,130 @@ def test_against_golden_fixtures(fb, name):
             m.lloyd(rho, max_iter=1, warm=True)
             assert np.abs(m.generators() - g[key]).max() < 1e-13
     m.close()
+
+
+@pytest.mark.parametrize("case", ["ico5_uniform", "u10242_x4", "fib20000_relaxed"])
+def test_quality_against_oracle(fb, O, case):
+    """fm_quality (degree histogram, cell / triangle areas by calc_area SG:198-227, triangle angles
+    by calc_sphere_angle SG:247-285, largest generator-to-centroid chord) against fo_quality.
+    Tolerances: histogram exact; areas and angles 1e-13 absolute (sums of <= 15 acos values of
+    O(1)); the two 4 pi sums 1e-10 (the reference's own threshold, MM:306/320); chord 1e-12."""
+    from fishman_b200 import points
+    if case == "ico5_uniform":
+        p, rg, ro = points.ico(5), fb.density_uniform(), O.density_uniform()
+    elif case == "u10242_x4":
+        p, rg, ro = points.uniform(10242, 0), fb.density_x4(), O.density_x4()
+    else:
+        p, rg, ro = points.fibonacci(20000, 3), fb.density_uniform(), O.density_uniform()
+    m = fb.Mesh.from_xyz(p)
+    if case == "fib20000_relaxed":
+        m.lloyd(rg, max_iter=3, warm=True)
+        p = m.generators()
+    else:
+        m.delaunay_triangulation()
+    q = m.quality(rg)
+    o = O.Oracle(p)
+    o.delaunay_triangulation(); o.voronoi_diagram()
+    oq = o.quality(ro)
+    assert q["degree_hist"] == oq["degree_hist"] and sum(q["degree_hist"]) == len(p)
+    for k in ("area_cell_min", "area_cell_max", "area_tri_min", "area_tri_max", "angle_min", "angle_max"):
+        assert abs(q[k] - oq[k]) < 1e-13, (k, q[k], oq[k])
+    for k in ("area_cell_sum", "area_tri_sum"):
+        assert abs(q[k] - oq[k]) < 1e-10 and abs(q[k] - 4 * np.pi) < 1e-10, (k, q[k], oq[k])
+    assert abs(q["max_disp"] - oq["max_disp"]) < TOL
+    g0 = m.generators()
+    q2 = m.quality(rg)
+    assert q2 == q and np.array_equal(m.generators(), g0)   # deterministic sums; nothing moved
+    it, md = m.lloyd(rg, max_iter=1, warm=True)
+    assert abs(md - q["max_disp"]) < 1e-15   # the chord fm_quality announced is the step Lloyd makes
+    m.close(); o.close()
+
+
+def test_lloyd_batches_equal_single_steps(fb):
+    """fm_lloyd queues its warm iterations in batches and reads the device back once per batch
+    (fm_iter_end takes the convergence / rebuild decisions on the device).  Same iteration count,
+    same displacement, bit-identical generators as one host round trip per iteration -- through a
+    rebuild in the middle (random start: triangles turn over in the first iterations) and through
+    the convergence test."""
+    from fishman_b200 import points
+    p = points.uniform(20000, 2)
+    a, b = fb.Mesh.from_xyz(p), fb.Mesh.from_xyz(p)
+    mds = [a.lloyd(max_iter=1, warm=True)[1] for _ in range(12)]
+    it, md = b.lloyd(max_iter=12, tol=0.0, warm=True)
+    assert it == 12 and md == mds[-1]
+    assert np.array_equal(a.generators(), b.generators())
+    sa, sb = a.stats(), b.stats()
+    assert sa["cold"] == sb["cold"] and sa["warm"] == sb["warm"] and sa["flips"] == sb["flips"]
+    assert sa["cold"] >= 2 and sa["warm"] >= 3          # both paths were taken
+    # convergence inside a batch: stop at the first iteration with max_disp <= tol
+    more = [a.lloyd(max_iter=1, warm=True)[1] for _ in range(40)]
+    tol = more[24] * 1.0000001
+    k = next(i for i, v in enumerate(more) if v <= tol) + 1
+    it, md = b.lloyd(max_iter=100, tol=tol, warm=True)
+    assert it == k and md == more[k - 1]
+    a.close(); b.close()
+
+
+@pytest.mark.parametrize("n", [40, 200, 2000, 20000])
+def test_retriangulate_warm_after_a_strong_move(fb, n):
+    """fm_retriangulate(h, warm=1) when triangles turned over: the failed repair has stamped
+    amark / vote, the rebuild must start on a fresh stamp (CPU twin:
+    tests/test_emu.py::test_rebuild_after_a_failed_warm_repair)."""
+    from fishman_b200 import points
+    for trial in range(20 if n <= 200 else 3):
+        rng = np.random.default_rng(1000 * n + trial)
+        p = points.uniform(n, trial)
+        q = p + 1.5 * np.sqrt(4 * np.pi / n) * rng.normal(size=p.shape)
+        q /= np.linalg.norm(q, axis=1)[:, None]
+        m = fb.Mesh.from_xyz(p)
+        m.delaunay_triangulation()
+        m.set_generators(q)
+        m.stats_reset()
+        m.retriangulate(warm=True)
+        assert m.stats()["cold"] == 1      # a triangle turned over: rebuilt
+        tri, adj = m.triangles()
+        _check.check_triangulation(q, tri, adj)
+        m2 = fb.Mesh.from_xyz(q)
+        m2.delaunay_triangulation()
+        assert np.array_equal(_check.canonical(tri), _check.canonical(m2.triangles()[0]))
+        m.close(); m2.close()
+
+
+def test_getters_follow_the_generators(fb):
+    """After fm_lloyd (ends with a centroid update) or fm_set_generators the getters repair the
+    connectivity first: triangles, Voronoi diagram and quality belong to the CURRENT generators."""
+    from fishman_b200 import points
+    p = points.fibonacci(6000, 2)
+    m = fb.Mesh.from_xyz(p)
+    m.lloyd(max_iter=4, warm=True)
+    g = m.generators()
+    m2 = fb.Mesh.from_xyz(g)
+    m2.delaunay_triangulation(); m2.voronoi_diagram()
+    assert np.array_equal(_check.canonical(m.triangles()[0]), _check.canonical(m2.triangles()[0]))
+    m.lloyd(max_iter=1, warm=True)
+    m.set_generators(g)
+    m.voronoi_diagram()
+    tri, _ = m.triangles()
+    tri2, _ = m2.triangles()
+    assert np.array_equal(_check.canonical(tri), _check.canonical(tri2))
+    assert _check.max_cc_diff(tri, m.circumcentres()[0], tri2, m2.circumcentres()[0]) == 0.0
+    m.close(); m2.close()
+
+
+def test_block_transfer_single_rank(fb):
+    """fm_block_ids / fm_get_generators_block / fm_set_generators_block on an unsharded handle: the
+    block is the whole set in internal order (the sharded form is checked by tools/dist_check.py)."""
+    from fishman_b200 import points
+    p = points.uniform(5000, 9)
+    m = fb.Mesh.from_xyz(p)
+    ids = m.block_ids()
+    assert np.array_equal(np.sort(ids), np.arange(1, len(p) + 1))
+    x, y, z = (np.empty(len(p)) for _ in range(3))
+    m.get_generators_block_soa(x, y, z)
+    assert np.array_equal(np.stack([x, y, z], 1), p[ids - 1])
+    q = points.uniform(5000, 10)
+    qb = np.ascontiguousarray(q[ids - 1].T)
+    m.set_generators_block_soa(qb[0], qb[1], qb[2])
+    assert np.array_equal(m.generators(), q)
+    m.delaunay_triangulation()
+    m.close()
