@@ -15,7 +15,7 @@ SYMBOLS = [
     "fm_get_mpas_edges_on_edge", "fm_lloyd", "fm_lloyd_local", "fm_generator_block", "fm_peer_handle", "fm_peer_attach", "fm_density_eval", "fm_get_generators",
     "fm_set_generators", "fm_host_alloc", "fm_host_free", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
     "fm_profile_enable", "fm_profile_get", "fm_device_info",
-    "fm_block_ids", "fm_get_generators_block", "fm_set_generators_block", "fm_quality",
+    "fm_fp64_peak", "fm_block_ids", "fm_get_generators_block", "fm_set_generators_block", "fm_quality",
 ]
 
 
@@ -84,6 +84,7 @@ def lib():
     L.fm_profile_enable.argtypes = [vp, i32]
     L.fm_profile_get.argtypes = [vp, i32, C.c_void_p, i64p, dp, i64p, ip]
     L.fm_device_info.argtypes = [C.c_char_p, i32, ip]
+    L.fm_fp64_peak.argtypes = [C.c_double, dp]
     L.fm_block_ids.argtypes = [vp, ip]
     L.fm_get_generators_block.argtypes = [vp, dp, dp, dp]
     L.fm_set_generators_block.argtypes = [vp, dp, dp, dp]

@@ -446,6 +446,19 @@ struct KSweepImpl {
 #endif
     body(c, item, t, c.row[t]);
   }
+#if defined(__CUDA_ARCH__)
+  // as run(), inside a batch of warm iterations: leaves when the batch has halted.  The halt
+  // word is loaded AFTER the row load has been issued and both are in flight together; a gate
+  // ahead of the row load would put one more memory latency at the head of every thread's chain.
+  __device__ static void run_gated(const DtCtx& c, int item) {
+    const int t = slot(c, item);
+    if (c.pf_dist > 0 && t + c.pf_dist < c.n_tri) asm volatile("prefetch.global.L2 [%0];" ::"l"(c.row + t + c.pf_dist));
+    const Row r = c.row[t];
+    const int hv = ((volatile const int*)c.counters)[FM_T_HALT];
+    if (hv != 0 && r.v.x >= 0) return;   // (the second term only ties the branch to the row load's issue slot)
+    body(c, item, t, r);
+  }
+#endif
   // the row is passed in so that a launcher can have the rows of several items in flight at once
   FM_HD static void body(const DtCtx& c, int item, int t, const Row& r) {
     I4 v = r.v, a = r.a;

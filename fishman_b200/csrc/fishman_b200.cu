@@ -1047,7 +1047,9 @@ static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded) {
 static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded, bool dry) {
   Density d = make_density(rho);
   VdCtx c = h->vd_ctx(&d);
-  c.abort_flag = guarded ? h->counters + 3 : nullptr;
+  // guarded (warm iteration): skipped when the batch has halted -- converged, error, or a triangle
+  // turned over (fm_flip_coop / fm_apply_requests' count turns that into the halt word)
+  c.abort_flag = guarded ? h->counters + FM_T_HALT : nullptr;
   int cnt = h->blk_count;
   if (dry) {  // fm_quality: every cell, nothing moved, nothing sent
     c.dry = 1; c.n_peers = 0; c.cell_begin = 0; c.cell_end = h->n; c.ringc = nullptr;
@@ -1504,6 +1506,36 @@ extern "C" int fm_debug_counters(fm_handle* h, int32_t* out) {
   return 0;
 }
 #endif
+// fp64 FMA rate of the current device in TFLOP/s: fm_dfma_chains on every SM, repeated until
+// at least min_ms of device time have been measured (CUDA events on the default stream).
+extern "C" int fm_fp64_peak(double min_ms, double* tflops) {
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess ||
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 1;
+  double* sink = nullptr;
+  cudaEvent_t e0, e1;
+  if (cudaMalloc((void**)&sink, sizeof(double)) != cudaSuccess) return 1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  const int blocks = sms * 8, threads = 256, iters = 4096;
+  const double flop_per_launch = 2.0 * 64.0 * iters * (double)blocks * threads;   // 64 DFMA per loop trip
+  fm_dfma_chains<<<blocks, threads>>>(16, 1.0, sink);   // warm-up
+  cudaDeviceSynchronize();
+  double best = 0.0, total_ms = 0.0;
+  for (int rep = 0; rep < 64 && (rep < 3 || total_ms < min_ms); rep++) {
+    cudaEventRecord(e0);
+    fm_dfma_chains<<<blocks, threads>>>(iters, 1.0 + rep, sink);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) break;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    total_ms += ms;
+    if (ms > 0 && flop_per_launch / (ms * 1e-3) / 1e12 > best) best = flop_per_launch / (ms * 1e-3) / 1e12;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+  if (tflops) *tflops = best;
+  return (best > 0.0 && cudaGetLastError() == cudaSuccess) ? 0 : 1;
+}
+
 extern "C" int fm_device_info(char* name, int32_t cap, int32_t* sms) {
   cudaDeviceProp p;
   int dev = 0;

@@ -18,14 +18,21 @@ __device__ __forceinline__ void use_device_stamp(VdCtx&) {}
 
 // A batch of warm Lloyd iterations is queued without the host looking in between
 // (fm_iter_end below).  Once an iteration of the batch converged, found a turned-over triangle
-// or hit an error, every later launch of the batch leaves at once; the same after a peer rank
-// missed a barrier (FM_E_PEER): the data of that iteration never arrived.
+// or hit an error (a peer rank that missed a barrier included), counters[FM_T_HALT] is set and
+// every later launch of the batch leaves at once.  ONE word, one load: the kernels of the warm
+// iteration are chains of dependent gathers, and a gate in front of the first gather is a
+// whole extra memory latency per thread (measured: sweep 0.115 -> 0.183 ms with a two-load
+// gate ahead of the row load) -- so the sweep issues its row load first and tests the word
+// while the row is in flight (KSweepImpl::run_gated), and the kernels of a cold build, which
+// never run in a halted batch, are not gated at all.
 __device__ __forceinline__ bool fm_halted(const int* counters) {
-  return counters && ((((volatile const int*)counters)[FM_T_HALT] != 0) ||
-                      ((((volatile const int*)counters)[FM_C_ERR] & FM_E_PEER) != 0));
+  return counters && ((volatile const int*)counters)[FM_T_HALT] != 0;
 }
 __device__ __forceinline__ bool fm_halted(const DtCtx& c) { return fm_halted(c.counters); }
 __device__ __forceinline__ bool fm_halted(const VdCtx& c) { return fm_halted(c.counters); }
+template <class K> struct KGated { static const bool value = false; };
+template <> struct KGated<KSweepT<false>> { static const bool value = true; };
+template <> struct KGated<KSweepShT<false>> { static const bool value = true; };
 
 // Resident 256-thread blocks per SM the launcher asks ptxas to make room for.  The gather
 // kernels are latency / L1 bound; their filter-only forms (K<false>) contain no calls and
@@ -40,14 +47,14 @@ template <> struct KOcc<KCheckT<false>> { static const int value = 4; };
 template <class K, class Ctx>
 __global__ void __launch_bounds__(256, KOcc<K>::value) fm_kernel(Ctx c, int n) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (fm_halted(c)) return;
   use_device_stamp(c);
-  if (i < n) K::run(c, i);
+  if (i >= n) return;
+  if constexpr (KGated<K>::value) K::run_gated(c, i);
+  else K::run(c, i);
 }
 // K over [0, counters[idx]): the count lives on the device, the host launches for an upper bound
 template <class K>
 __global__ void __launch_bounds__(256) fm_kernel_counted(DtCtx c, int idx) {
-  if (fm_halted(c)) return;
   use_device_stamp(c);
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < c.counters[idx]) K::run(c, i);
@@ -80,7 +87,11 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
   volatile int* vc = c.counters;
   int stamp = vc[FM_C_STAMP];
   if (fm_halted(c)) return;
-  if (vc[3] > 0) return;  // a triangle turned over: leave everything to the rebuild
+  if (vc[3] > 0) {  // a triangle turned over: leave everything to the rebuild (and stop the batch: the
+                    // centroid stage tests the one halt word)
+    if (gid == 0) vc[FM_T_HALT] = FM_HALT_REBUILD;
+    return;
+  }
   int sub = 0, maxq = 0;
   for (;; sub++) {
     int nact = vc[cur];
@@ -161,8 +172,7 @@ __global__ void fm_subround_end(int* counters, int cur, int nact) {
 template <bool UNIFORM>
 __global__ void __launch_bounds__(128, UNIFORM ? FM_OCC_CENTROID : FM_OCC_CENTROID_RHO) fm_centroid_update(const VdCtx c, int n) {
   extern __shared__ int ring_smem[];
-  if (fm_halted(c)) return;
-  if (c.abort_flag && *c.abort_flag) return;
+  if (c.abort_flag && *(volatile const int*)c.abort_flag) return;  // = the halt word (launch_centroid_kernel)
   int j = blockIdx.x * blockDim.x + threadIdx.x;
   double disp = 0.0;
   if (j < n) disp = KCentroid::compute<UNIFORM>(c, c.cell_begin + j, ring_smem + threadIdx.x, blockDim.x);
@@ -229,7 +239,11 @@ __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
     *(volatile int*)&pc.sync[k]->flag[pc.rank] = e;
     long long t0 = clock64();
     while (*(volatile int*)&self->flag[k] < e) {
-      if (clock64() - t0 > pc.timeout_cycles) { atomicOr(counters + FM_C_ERR, FM_E_PEER); break; }
+      if (clock64() - t0 > pc.timeout_cycles) {  // the data of this iteration never arrived: nothing may use it
+        atomicOr(counters + FM_C_ERR, FM_E_PEER);
+        ((volatile int*)counters)[FM_T_HALT] = FM_HALT_ERROR;
+        break;
+      }
     }
   }
   __syncthreads();
@@ -434,6 +448,24 @@ __global__ void fm_block_pack_fan(int cnt, const double* x, const double* y, con
   P4 q = f.dst[0][i];           // keeps the id
   q.x = x[i]; q.y = y[i]; q.z = z[i];
   for (int k = 0; k < f.n_dst; k++) f.dst[k][i] = q;
+}
+
+// ---- measurement support: the fp64 FMA rate of this GPU (fm_fp64_peak).  Eight independent DFMA
+// chains per thread (a DFMA's result is usable after ~8 cycles; 8 chains x 8 warps per scheduler
+// keep the pipe full), 256 threads x 8 blocks per SM, no memory traffic.
+__global__ void __launch_bounds__(256) fm_dfma_chains(int iters, double seed, double* sink) {
+  double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 0.999999, b = 1.0e-9;
+#pragma unroll 1
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      a0 = fma(a0, m, b); a1 = fma(a1, m, b); a2 = fma(a2, m, b); a3 = fma(a3, m, b);
+      a4 = fma(a4, m, b); a5 = fma(a5, m, b); a6 = fma(a6, m, b); a7 = fma(a7, m, b);
+    }
+  }
+  double s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (s == 123.456) *sink = s;   // never true: keeps the chains alive
 }
 
 // duplicates share a Morton key, so they sit in one run of equal keys

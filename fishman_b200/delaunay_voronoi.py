@@ -57,6 +57,14 @@ def _i(a):
     return a.ctypes.data_as(C.POINTER(C.c_int32))
 
 
+def fp64_peak_tflops(min_ms=60.0):
+    """fp64 FMA rate of the current GPU measured now (fm_fp64_peak), TFLOP/s."""
+    v = C.c_double(0.0)
+    if _lib.lib().fm_fp64_peak(float(min_ms), C.byref(v)):
+        raise FishmanError("fm_fp64_peak failed")
+    return v.value
+
+
 def pinned_empty(n):
     """float64 array of n elements in page-locked host memory (fm_host_alloc); kept alive
     for the life of the process."""
@@ -162,6 +170,12 @@ class Mesh:
         vc = np.empty((self.n_edge, 2), dtype=np.int32)
         self._chk(_lib.lib().fm_get_edges(self._h, _i(de), _i(vv), _i(vc)))
         return de, vv, vc
+
+    def mpas_device_only(self, strict=False):
+        """fm_mpas without bringing anything back to the host (timing); returns maxEdges."""
+        me = C.c_int32(0)
+        self._chk(_lib.lib().fm_mpas(self._h, 1 if strict else 0, C.byref(me)))
+        return me.value
 
     def mpas(self, strict=True):
         """mpas_mesh_adapt + calc_weightsOnEdge (src/mpas_mesh_mod.F90:181-345, :442-561) on the

@@ -197,6 +197,10 @@ int fm_stats_reset(fm_handle* h);
 int fm_profile_enable(fm_handle* h, int32_t on);
 int fm_profile_get(fm_handle* h, int32_t cap, char (*names)[32], int64_t* launches, double* ms,
                    int64_t* threads, int32_t* rows);
+/* fp64 FMA rate of the device in use, TFLOP/s: independent DFMA chains on every SM, repeated until
+ * at least min_ms of device time were measured; the best launch is reported.  The denominator of
+ * the fp64-pipe roofline of the centroid / quadrature kernel (no fp64 peak is published for the box). */
+int fm_fp64_peak(double min_ms, double* tflops);
 /* name and SM count of the device in use */
 int fm_device_info(char* name, int32_t cap, int32_t* sms);
 

@@ -183,8 +183,23 @@ def test_c4_2621442_against_oracle():
     o.close()
     it, md = m.lloyd(fb.density_uniform(), max_iter=1, warm=True)
     g1 = m.generators()
-    assert np.abs(g1 - og).max() < 1e-12
-    assert abs(md - np.linalg.norm(og - p, axis=1).max()) < 1e-12
+    # Inside a band quad the reference may keep the diagonal that is NOT Delaunay (it abstains,
+    # DV:878-880); the four cells around such a quad then get a ring of circumcentres that is not
+    # their Voronoi cell, and their centroids differ from the true ones by far more than round-off
+    # (measured 1.4e-8 on a thin quad).  Those cells -- the vertices of the differing triangles, at
+    # most four per explained quad -- are compared loosely and counted; every other cell at 1e-12.
+    touched = np.zeros(n, dtype=bool)
+    if r["n_diff"]:
+        only = np.setdiff1d(np.arange(len(tri)), r["common_a"])
+        touched[np.unique(tri[only].astype(np.int64) - 1)] = True
+    err = np.abs(g1 - og).max(axis=1)
+    print("C4: cells around band quads", int(touched.sum()), "max generator diff there",
+          float(err[touched].max()) if touched.any() else 0.0, "elsewhere", float(err[~touched].max()))
+    assert touched.sum() <= 2 * r["n_diff"]
+    assert err[~touched].max() < 1e-12
+    assert (err[touched] < 1e-6).all()
+    omd = np.linalg.norm(og - p, axis=1)
+    assert abs(md - omd[~touched].max()) < 1e-12 or abs(md - omd.max()) < 1e-12
     assert m.stats()["warm"] == 1      # the step ran on the triangulation compared above
     m.close()
 

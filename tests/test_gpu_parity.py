@@ -359,7 +359,7 @@ def test_getters_follow_the_generators(fb):
     tri, _ = m.triangles()
     tri2, _ = m2.triangles()
     assert np.array_equal(_check.canonical(tri), _check.canonical(tri2))
-    assert _check.max_cc_diff(tri, m.circumcentres()[0], tri2, m2.circumcentres()[0]) == 0.0
+    assert _check.max_cc_diff(tri, m.circumcentres()[0], tri2, m2.circumcentres()[0]) < 1e-15   # vertex rotation of a slot differs
     m.close(); m2.close()
 
 
