@@ -23,6 +23,7 @@ module fishman_gpu_c
   public :: fm_mpas, fm_get_mpas_edges, fm_get_mpas_cells, fm_get_mpas_vertices, fm_get_mpas_edges_on_edge
   public :: fm_lloyd, fm_lloyd_local, fm_generator_block, fm_peer_handle, fm_peer_attach
   public :: fm_get_generators, fm_set_generators, fm_density_eval
+  public :: fm_quality_stats, fm_quality, fm_block_ids, fm_get_generators_block, fm_set_generators_block, fm_fp64_peak
   public :: fm_error_message
 
   ! typedef struct fm_density { int32_t kind; double cx, cy, cz, beta, alpha, gamma; }
@@ -31,6 +32,15 @@ module fishman_gpu_c
     real(c_double) :: cx = 0.0d0, cy = 0.0d0, cz = 1.0d0
     real(c_double) :: beta = 0.0d0, alpha = 1.0d0, gamma = 1.0d0
   end type fm_density
+
+  ! typedef struct fm_quality_stats (mesh-quality statistics, SURVEY.md 7.3)
+  type, bind(C) :: fm_quality_stats
+    integer(c_int64_t) :: degree_hist(16)
+    real(c_double) :: area_cell_min, area_cell_max, area_cell_sum
+    real(c_double) :: area_tri_min, area_tri_max, area_tri_sum
+    real(c_double) :: angle_min, angle_max
+    real(c_double) :: max_disp
+  end type fm_quality_stats
 
   interface
 
@@ -214,6 +224,38 @@ module fishman_gpu_c
       type(c_ptr), value :: h
       real(c_double), intent(in) :: x(*), y(*), z(*)
     end function fm_set_generators
+
+    integer(c_int) function fm_quality(h, rho, q) bind(C, name='fm_quality')
+      import :: c_int, c_ptr, fm_density, fm_quality_stats
+      type(c_ptr), value :: h
+      type(fm_density), intent(in) :: rho
+      type(fm_quality_stats), intent(out) :: q
+    end function fm_quality
+
+    ! one rank's block of a sharded mesh (fm_create_dist): ids, download, upload
+    integer(c_int) function fm_block_ids(h, ids) bind(C, name='fm_block_ids')
+      import :: c_int, c_int32_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int32_t), intent(out) :: ids(*)
+    end function fm_block_ids
+
+    integer(c_int) function fm_get_generators_block(h, x, y, z) bind(C, name='fm_get_generators_block')
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      real(c_double), intent(out) :: x(*), y(*), z(*)
+    end function fm_get_generators_block
+
+    integer(c_int) function fm_set_generators_block(h, x, y, z) bind(C, name='fm_set_generators_block')
+      import :: c_int, c_double, c_ptr
+      type(c_ptr), value :: h
+      real(c_double), intent(in) :: x(*), y(*), z(*)
+    end function fm_set_generators_block
+
+    integer(c_int) function fm_fp64_peak(min_ms, tflops) bind(C, name='fm_fp64_peak')
+      import :: c_int, c_double
+      real(c_double), value :: min_ms
+      real(c_double), intent(out) :: tflops
+    end function fm_fp64_peak
 
   end interface
 
