@@ -9,7 +9,6 @@
 //                                         (= launch_filtered<KLocateVoteT>, or its sharded form)
 //   Backend::fill64(ptr, value, count)    device memset of 64-bit words
 //   Backend::fill32(ptr, value, count)
-//   Backend::exclusive_scan(ptr, n)       in place over ints; returns the total
 //   Backend::launch_counted<K>(ctx, idx, upper)  K::run(ctx, i) for i in [0, counters[idx]), a count the host
 //                                         only knows an upper bound of
 //   Backend::read_ints(dst, src, n)       device -> host (synchronising)
@@ -216,10 +215,15 @@ inline int dt_level_count(int n) {
 // use).  listA/listB: two int queues of 2n-4 entries.  lvl_order: the points sorted by
 // (level, internal index); lvl_off (host, K+2 entries): start of each level in lvl_order,
 // level L = class K-L; prev: scratch of n ints; boot: the four bootstrap points.
+// lvl_pos: the inverse of lvl_order (position of every point).
 template <class B>
-int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const int* lvl_off, int K,
+int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const int* lvl_pos, const int* lvl_off, int K,
            int* prev, const int boot[4], int* stamp, DtStats* st, char* msg, size_t msglen) {
   c.n_tri = 4;
+  c.lvl_order = lvl_order;
+  c.wlist = c.fliplist;  // n-1 entries: every split of a build fits; the flip rounds use it after the split is done
+  for (int k = 0; k < 4; k++) be.read_ints(&c.boot_pos[k], lvl_pos + boot[k], 1);
+  be.fill64(c.winner, kNone64, 2 * (size_t)c.n - 4);
   memset(st, 0, sizeof *st);
   int zero[15] = {0}, host[8];
   int* list[2] = {listA, listB};
@@ -264,16 +268,17 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
     // the voters: this level, and with leftovers all levels before it (inserted points leave at once)
     const int lo = carry > 0 ? 0 : L;
     c.plist = lvl_order + lvl_off[lo];
+    c.plist_off = lvl_off[lo];
     m = lvl_off[L + 1] - lvl_off[lo];
     c.n_plist = m;
     remaining += carry;
     for (int rounds_here = 0; remaining > 0 && (L == K || rounds_here < kRoundsPerLevel); rounds_here++) {
       st->rounds++;
-      be.fill64(c.winner, kNone64, (size_t)c.n_tri);
       be.locate_round(c, m);
-      be.template launch<KSplitFlag>(c, c.n_tri);
-      int nsplit = be.exclusive_scan(c.rank, c.n_tri);
-      be.read_ints(host, c.err, 1);
+      // ONE readback per round: the number of triangles that received a vote (= splits) and the error bits
+      be.read_ints(host, c.counters + FM_C_ERR, 2);
+      static_assert(FM_C_NWIN == FM_C_ERR + 1, "one readback for both");
+      const int nsplit = host[1];
       if (host[0]) {
         snprintf(msg, msglen, "point location failed (error bits %d): duplicate points?", host[0]);
         return 1;
@@ -285,7 +290,13 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
       c.stamp = *stamp;
       c.next_active = list[0];
       c.qcount = c.counters;
-      be.template launch<KSplit>(c, c.n_tri);
+      // the splits run over the winner list; its length is on the device, the host knows it too by now
+      be.template launch_counted<KSplit>(c, FM_C_NWIN, nsplit);
+      be.template launch_counted<KWinnerReset>(c, FM_C_NWIN, nsplit);
+      {
+        int zero1 = 0;
+        be.write_ints(c.counters + FM_C_NWIN, &zero1, 1);
+      }
       if (getenv("FM_DEBUG_ROUNDS")) {
         fprintf(stderr, "level %d round %d: voters %d pool %d inserted %d triangles %d", L, rounds_here, m,
                 remaining, nsplit, c.n_tri);

@@ -64,6 +64,8 @@ enum {
   FM_C_MAXDISP = 10,   // 64-bit word: bits of the largest chord displacement ([10], [11])
   FM_C_ERR = 12,       // error bits (DtCtx::err points here in the CUDA library)
   FM_C_REQ = 13,       // sharded sweep: flip requests this rank found
+  FM_C_NWIN = 13,      // cold build (no sharded sweep runs then): triangles that received a first vote this
+                       // round = entries of DtCtx::wlist = splits of the round
   FM_C_BND = 14,       // sharded sweep: swept triangles with a vertex owned by another rank
   FM_C_STAMP = 15,     // next unused stamp
   // [16..31]: state of a BATCH of warm Lloyd iterations queued without a host round trip
@@ -103,15 +105,20 @@ struct DtCtx {
   const int* plist;            // points taking part in this round (the current insertion level), or
                                // null = all points; thread i of the locate kernels handles plist[i]
   int n_plist;
+  const int* lvl_order;        // all points sorted by (level, internal index); plist = lvl_order + plist_off
+  int plist_off;
+  int boot_pos[4];             // positions of the four bootstrap points in lvl_order
+  int* wlist;                  // triangles that received their first vote this round (length counters[FM_C_NWIN])
   int locate_only;             // sharded point location: walk and record loc[], the votes are cast later (KVote)
   const int* prev;             // per point: nearest point to the left (internal order) of a coarser level
   const int* next_rev;         // the same to the right, stored reversed: next_rev[n-1-i] = n-1-j for the
                                // smallest j >= i of a coarser level, or -1 (null = left side only)
   int level_thr;               // coarseness of the current level
   int level_max;               // coarsest class K
-  u64* winner;                 // per triangle: min over its points of (priority << 32 | point)
-  int* rank;                   // per triangle: exclusive scan of "splits this round"
-  int n_tri;                   // triangles alive at the start of the round
+  u64* winner;                 // per triangle: min over its points of (priority << 32 | position of the point in
+                               // lvl_order); all ones between rounds
+  int* rank;                   // scratch of 2n-3 ints (the winner list lives here)
+  int n_tri;                   // triangles alive (host bookkeeping; the final count is 2n-4)
   // flip rounds
   int stamp;                   // global sub-round counter (>= 1)
   const int* stamp_dev;        // when non-null the device-resident stamp (counters[FM_C_STAMP]) overrides
@@ -291,6 +298,15 @@ struct KLevelInit {
 #if defined(FM_COUNT_STEPS) && !defined(__CUDACC__)
 static long long fm_walk_stats[3];  // triangles visited, walks, walks longer than 30 steps
 #endif
+// The vote of the point at position lp of lvl_order (original id qi) for triangle t.  The first
+// vote a triangle receives in a round puts it on the winner list: the split then runs over that
+// list instead of over all triangle slots.
+FM_HD inline void cast_vote(const DtCtx& c, int t, int qi, int lp) {
+  u64 key = ((u64)hash32((unsigned)qi) << 32) | (unsigned)lp;
+  u64 old = FM_ATOMIC_MIN64(&c.winner[t], key);
+  if (old == kNone64) c.wlist[FM_ATOMIC_ADD32(&c.counters[FM_C_NWIN], 1)] = t;
+}
+
 template <bool EXACT>
 struct KLocateVoteT {
   FM_HD static void run(const DtCtx& c, int i) {
@@ -325,8 +341,7 @@ struct KLocateVoteT {
     fm_walk_stats[0] += steps + 1; fm_walk_stats[1] += 1; fm_walk_stats[2] += steps > 30;
 #endif
     if (c.locate_only) return;
-    u64 key = ((u64)hash32((unsigned)qi) << 32) | (unsigned)p;
-    FM_ATOMIC_MIN64(&c.winner[t], key);
+    cast_vote(c, t, qi, c.plist_off + i);
   }
 };
 typedef KLocateVoteT<true> KLocateVote;
@@ -338,41 +353,45 @@ struct KVote {
     int p = c.plist ? c.plist[i] : i;
     int t = c.loc[p];
     if (t < 0) return;
-    u64 key = ((u64)hash32((unsigned)c.pts[p].id) << 32) | (unsigned)p;
-    FM_ATOMIC_MIN64(&c.winner[t], key);
+    cast_vote(c, t, (int)c.pts[p].id, c.plist_off + i);
   }
-};
-
-// One thread per triangle: 1 if it splits this round (input of the scan).
-struct KSplitFlag {
-  FM_HD static void run(const DtCtx& c, int t) { c.rank[t] = (c.winner[t] != kNone64) ? 1 : 0; }
 };
 
 // ------------------------------------------------------------------ 1->3 split
-// One thread per triangle that won a point p.  (a,b,c) becomes
+// One thread per entry of the winner list: triangle t won the point p.  (a,b,c) becomes
 //   A = (a,b,p) in slot t,  B = (b,c,p) in slot s1,  C = (c,a,p) in slot s1+1,
 // the new vertex always last (as DV:977-982), so the edge inherited from the
-// parent is edge 2 of each child.  A neighbour that splits in the same launch is
-// not touched: where ITS child will be follows from its winner and rank alone.
+// parent is edge 2 of each child.  The two new slots belong to the POINT, not to the round:
+// s1 = 4 + 2 * (position of p in lvl_order, the bootstrap points not counted).  No scan over the
+// triangles, no count the host has to wait for, and a slot numbering that depends on nothing
+// but the input (the ranks of a sharded mesh hold slot-for-slot identical replicas).  A
+// neighbour that splits in the same launch is not touched: where ITS child will be follows from
+// its winner alone.
 struct KSplit {
-  FM_HD static int child_slot(const DtCtx& c, int n, int e) {
-    // slot of the child of (splitting) triangle n that inherits n's edge e
-    int s1 = c.n_tri + 2 * c.rank[n];
+  FM_HD static int slot_of(const DtCtx& c, int lp) {
+    int before = (c.boot_pos[0] < lp) + (c.boot_pos[1] < lp) + (c.boot_pos[2] < lp) + (c.boot_pos[3] < lp);
+    return 4 + 2 * (lp - before);
+  }
+  FM_HD static int child_slot(const DtCtx& c, int n, u64 wn, int e) {
+    // slot of the child of (splitting) triangle n, won by wn, that inherits n's edge e
+    int s1 = slot_of(c, (int)(wn & 0xffffffffULL));
     return e == 2 ? n : (e == 0 ? s1 : s1 + 1);
   }
-  FM_HD static void run(const DtCtx& c, int t) {
+  FM_HD static void run(const DtCtx& c, int i) {
+    int t = c.wlist[i];
     u64 w = c.winner[t];
-    if (w == kNone64) return;
-    int p = (int)(w & 0xffffffffULL);
+    int lp = (int)(w & 0xffffffffULL);
+    int p = c.lvl_order[lp];
     Row r = c.row[t];
     I4 v = r.v, a = r.a;
-    int s1 = c.n_tri + 2 * c.rank[t], s2 = s1 + 1;
+    int s1 = slot_of(c, lp), s2 = s1 + 1;
     int childOf[3] = {s1, s2, t};  // parent edge k -> child slot
     int outer[3];
     for (int k = 0; k < 3; k++) {
       int ne = geti(a, k), n = ne >> 2, e = ne & 3;
-      if (c.winner[n] != kNone64) {
-        outer[k] = enc(child_slot(c, n, e), 2);
+      u64 wn = c.winner[n];
+      if (wn != kNone64) {
+        outer[k] = enc(child_slot(c, n, wn, e), 2);
       } else {
         outer[k] = ne;
         ((int*)&c.row[n].a)[e] = enc(childOf[k], 2);
@@ -389,6 +408,10 @@ struct KSplit {
     queue_active(c, s2, c.stamp);
     FM_ATOMIC_ADD32(&c.counters[4], 1);
   }
+};
+// after the split: the winners of the round are consumed (all ones again)
+struct KWinnerReset {
+  FM_HD static void run(const DtCtx& c, int i) { c.winner[c.wlist[i]] = kNone64; }
 };
 
 // ---------------------------------------------------------------- flip rounds

@@ -392,6 +392,10 @@ __global__ void fm_level_offsets(int n, const unsigned* sorted_key, int K, int* 
   }
   off[L] = lo;
 }
+__global__ void fm_invert_perm(int n, const int* order, int* pos) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) pos[order[i]] = i;
+}
 __global__ void fm_prev_keys(int n, const P4* pts, int K, int thr, int* prev, int* next_rev) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {

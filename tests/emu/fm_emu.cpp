@@ -49,11 +49,6 @@ struct HostBackend {
   }
   void fill64(u64* p, u64 v, size_t n) { std::fill(p, p + n, v); }
   void fill32(int* p, int v, size_t n) { std::fill(p, p + n, v); }
-  int exclusive_scan(int* p, int n) {
-    int acc = 0;
-    for (int i = 0; i < n; i++) { int v = p[i]; p[i] = acc; acc += v; }
-    return acc;
-  }
   void read_ints(int* dst, const int* src, int n) { memcpy(dst, src, sizeof(int) * n); }
   void write_ints(int* dst, const int* src, int n) { memcpy(dst, src, sizeof(int) * n); }
   int argmax_dot(const DtCtx& c, const double* d) {
@@ -140,19 +135,20 @@ struct EmuMesh {
     c.n = n; c.pts = pts.data(); c.v2t = v2t.data();
     c.row = row.data(); c.loc = loc.data(); c.winner = winner.data();
     c.rank = rank.data(); c.vote = vote.data(); c.flip_edge = flip_edge.data(); c.role = role.data();
-    c.mailbox = mailbox.data(); c.amark = amark.data(); c.fliplist = fliplist.data(); c.counters = counters; c.err = &err; c.slow = slow.data();
+    c.mailbox = mailbox.data(); c.amark = amark.data(); c.fliplist = fliplist.data(); c.counters = counters; c.err = &counters[FM_C_ERR]; c.slow = slow.data();
     int boot[4];
     if (dt_bootstrap(be, c, boot, g_err, sizeof g_err)) return 1;
     for (int k = 0; k < 4; k++) loc[boot[k]] = -1;
     int K = dt_level_count(n);
-    std::vector<int> order(n), off(K + 2, 0), prev(n);
+    std::vector<int> order(n), off(K + 2, 0), prev(n), pos(n);
     std::iota(order.begin(), order.end(), 0);
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
       return point_class(pts[a].id, K) > point_class(pts[b].id, K);  // level = K - class, ascending
     });
+    for (int i = 0; i < n; i++) pos[order[i]] = i;
     for (int i = 0; i < n; i++) off[K - point_class(pts[i].id, K) + 1]++;
     for (int L = 0; L <= K; L++) off[L + 1] += off[L];
-    if (dt_run(be, c, listA.data(), listB.data(), order.data(), off.data(), K, prev.data(), boot, &stamp, &st,
+    if (dt_run(be, c, listA.data(), listB.data(), order.data(), pos.data(), off.data(), K, prev.data(), boot, &stamp, &st,
                g_err, sizeof g_err))
       return 1;
     if (c.n_tri != T) { snprintf(g_err, sizeof g_err, "triangle count %d != 2n-4", c.n_tri); return 1; }
@@ -242,7 +238,7 @@ extern "C" int fme_repair(int n, const double* xyz_old, const double* xyz_new, i
     if (bad == 0 && m.be.flip_loop(c, list, 0, true, &m.stamp, &m.st, g_err, sizeof g_err, -1)) return 1;
   }
   *turned = c.counters[3];
-  if (m.err) { snprintf(g_err, sizeof g_err, "error bits %d", m.err); return 1; }
+  if (m.counters[FM_C_ERR]) { snprintf(g_err, sizeof g_err, "error bits %d", m.counters[FM_C_ERR]); return 1; }
   m.export_tris(tri_out, adj_out);
   return 0;
 }
@@ -264,10 +260,10 @@ extern "C" int fme_rebuild_after_failed_repair(int n, const double* xyz_old, con
   m.be.emulate_abort = true;
   if (dt_repair_async(m.be, m.c, m.listA.data(), m.listB.data(), &m.stamp, &m.st, g_err, sizeof g_err)) return 1;
   *turned = m.c.counters[3];
-  m.err = 0;
+  m.counters[FM_C_ERR] = 0;
   m.be.skip_bump = skip_bump != 0;
   if (m.run()) return 1;
-  if (m.err) { snprintf(g_err, sizeof g_err, "error bits %d", m.err); return 1; }
+  if (m.counters[FM_C_ERR]) { snprintf(g_err, sizeof g_err, "error bits %d", m.counters[FM_C_ERR]); return 1; }
   m.export_tris(tri_out, adj_out);
   return 0;
 }

@@ -61,6 +61,25 @@ def main():
     md_a = [a.lloyd(rho, max_iter=1, warm=True)[1] for _ in range(iters)]
     g_a = a.generators()
     st_a = a.stats()
+    # the same iterations as ONE batched call (no host round trip between iterations), and the
+    # per-rank block transfer: every rank uploads / downloads only the cells it owns
+    c = fb.Mesh.from_xyz(p, rank=rank, size=world)
+    c.peer_connect(dist)
+    it_c, md_c = c.lloyd(rho, max_iter=iters, tol=0.0, warm=True)
+    batch_equal = it_c == iters and md_c == md_ref[-1] and np.array_equal(c.generators(), g_ref)
+    ids = c.block_ids()
+    hb = [np.empty(max(len(ids), 1)) for _ in range(3)]
+    c.get_generators_block_soa(*hb)
+    block_get_ok = len(ids) == 0 or np.array_equal(np.stack([v[:len(ids)] for v in hb], 1), g_ref[ids - 1])
+    pb = np.ascontiguousarray(p[ids - 1].T) if len(ids) else np.zeros((3, 1))
+    c.set_generators_block_soa(pb[0].copy(), pb[1].copy(), pb[2].copy())     # every rank re-uploads its block of the START set
+    block_set_ok = np.array_equal(c.generators(), p)
+    it_c, md_c = c.lloyd(rho, max_iter=iters, tol=0.0, warm=True)
+    block_set_ok = block_set_ok and np.array_equal(c.generators(), g_ref)
+    all_ids = [None] * world
+    dist.all_gather_object(all_ids, ids.tolist())
+    cover_ok = sorted(v for part in all_ids for v in part) == list(range(1, n + 1))
+    c.close()
     a.retriangulate(warm=False)
     tri_a = fb.canonical_triangles(a.triangles()[0])
     a.close()
@@ -77,7 +96,9 @@ def main():
     b.close()
 
     print(f"rank {rank}: sharded cold build == single, slot for slot: {cold_equal}" + (f"; {prof}" if prof else ""), flush=True)
-    ok = cold_equal and (np.array_equal(g_ref, g_a) and np.array_equal(g_ref, g_b) and md_ref == md_a and md_ref == md_b)
+    print(f"rank {rank}: batched loop == single {batch_equal}; block download {block_get_ok}, block upload + rerun "
+          f"{block_set_ok}, blocks cover every cell once {cover_ok}", flush=True)
+    ok = cold_equal and batch_equal and block_get_ok and block_set_ok and cover_ok and (np.array_equal(g_ref, g_a) and np.array_equal(g_ref, g_b) and md_ref == md_a and md_ref == md_b)
     print(f"rank {rank}/{world}: n={n} iters={iters} p2p==single {np.array_equal(g_ref, g_a)} "
           f"nccl==single {np.array_equal(g_ref, g_b)} maxdisp equal {md_ref == md_a and md_ref == md_b} "
           f"last maxdisp {md_ref[-1]:.3e}", flush=True)
