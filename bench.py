@@ -286,15 +286,18 @@ def extra_cold(fb, p, rho, steps, peak):
     single-shot reference API would do."""
     m = fb.Mesh.from_xyz(p)
     m.lloyd(rho, max_iter=2, warm=False)
+    clk = ClockSampler(0)
+    clk.start()
     m.timer_begin()
     m.lloyd(rho, max_iter=steps, warm=False)
     ms = m.timer_end()
+    clocks = clk.stop()
     _, rows = profiled(m, lambda: m.lloyd(rho, max_iter=steps, warm=False))
     st = m.stats()
     m.close()
     n = len(p)
     per = ms / steps
-    return {"mode": "cold", "value": steps / (ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": per,
+    return {"mode": "cold", "value": steps / (ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": per, "clocks": clocks,
             "launches_per_step": st["launches"] / steps, "insertion_rounds_per_build": st["rounds"] / steps,
             "roofline": {"bound": "hbm", "scope": "whole iteration", "alg_bytes_per_item": ALG_BYTES["lloyd_iteration"],
                          "items": n, "achieved": ALG_BYTES["lloyd_iteration"] * n / (per * 1e-3) / 1e9, "peak": peak,
@@ -309,17 +312,20 @@ def extra_m2(fb, n, kind, peak, reps=3):
     del p
     m.delaunay_triangulation()
     ts = []
+    clk = ClockSampler(0)
+    clk.start()
     for _ in range(reps):
         m.timer_begin()
         m.retriangulate(warm=False)
         ts.append(m.timer_end())
+    clocks = clk.stop()
     _, rows = profiled(m, lambda: m.retriangulate(warm=False))
     st = m.stats()
     m.close()
     ms = float(np.median(ts))
     ach = ALG_BYTES["delaunay"] * n / (ms * 1e-3) / 1e9
     return {"points": n, "input": "U(N,0)" if kind == "uniform" else "FIB(N)+0.2h jitter", "value": n / (ms * 1e-3) / 1e6,
-            "unit": "Mpts/s", "ms": ms, "ms_all": [round(t, 3) for t in ts], "launches": st["launches"],
+            "unit": "Mpts/s", "ms": ms, "ms_all": [round(t, 3) for t in ts], "clocks": clocks, "launches": st["launches"],
             "insertion_rounds": st["rounds"], "flips": st["flips"],
             "roofline": {"bound": "hbm", "scope": "whole build", "alg_bytes_per_item": ALG_BYTES["delaunay"], "items": n,
                          "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak},

@@ -84,10 +84,15 @@ def lib():
     L.fm_profile_enable.argtypes = [vp, i32]
     L.fm_profile_get.argtypes = [vp, i32, C.c_void_p, i64p, dp, i64p, ip]
     L.fm_device_info.argtypes = [C.c_char_p, i32, ip]
-    L.fm_fp64_peak.argtypes = [C.c_double, dp]
-    L.fm_block_ids.argtypes = [vp, ip]
-    L.fm_get_generators_block.argtypes = [vp, dp, dp, dp]
-    L.fm_set_generators_block.argtypes = [vp, dp, dp, dp]
-    L.fm_quality.argtypes = [vp, C.POINTER(Density), C.POINTER(QualityStats)]
+    if hasattr(L, 'fm_fp64_peak'):   # absent from older builds loaded through FM_LIB (A/B runs)
+        L.fm_fp64_peak.argtypes = [C.c_double, dp]
+    if hasattr(L, 'fm_block_ids'):   # absent from older builds loaded through FM_LIB (A/B runs)
+        L.fm_block_ids.argtypes = [vp, ip]
+    if hasattr(L, 'fm_get_generators_block'):   # absent from older builds loaded through FM_LIB (A/B runs)
+        L.fm_get_generators_block.argtypes = [vp, dp, dp, dp]
+    if hasattr(L, 'fm_set_generators_block'):   # absent from older builds loaded through FM_LIB (A/B runs)
+        L.fm_set_generators_block.argtypes = [vp, dp, dp, dp]
+    if hasattr(L, 'fm_quality'):   # absent from older builds loaded through FM_LIB (A/B runs)
+        L.fm_quality.argtypes = [vp, C.POINTER(Density), C.POINTER(QualityStats)]
     _lib = L
     return L

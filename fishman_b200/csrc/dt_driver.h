@@ -11,6 +11,7 @@
 //   Backend::fill32(ptr, value, count)
 //   Backend::launch_counted<K>(ctx, idx, upper)  K::run(ctx, i) for i in [0, counters[idx]), a count the host
 //                                         only knows an upper bound of
+//   Backend::exclusive_scan_async(ptr, n) in place over ints, no host round trip
 //   Backend::read_ints(dst, src, n)       device -> host (synchronising)
 //   Backend::write_ints(dst, src, n)      host -> device
 //   Backend::argmax_dot(ctx, d)           index of the point with the largest p . d
@@ -215,15 +216,12 @@ inline int dt_level_count(int n) {
 // use).  listA/listB: two int queues of 2n-4 entries.  lvl_order: the points sorted by
 // (level, internal index); lvl_off (host, K+2 entries): start of each level in lvl_order,
 // level L = class K-L; prev: scratch of n ints; boot: the four bootstrap points.
-// lvl_pos: the inverse of lvl_order (position of every point).
 template <class B>
-int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const int* lvl_pos, const int* lvl_off, int K,
+int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const int* lvl_off, int K,
            int* prev, const int boot[4], int* stamp, DtStats* st, char* msg, size_t msglen) {
   c.n_tri = 4;
-  c.lvl_order = lvl_order;
   c.wlist = c.fliplist;  // n-1 entries: every split of a build fits; the flip rounds use it after the split is done
-  for (int k = 0; k < 4; k++) be.read_ints(&c.boot_pos[k], lvl_pos + boot[k], 1);
-  be.fill64(c.winner, kNone64, 2 * (size_t)c.n - 4);
+  be.fill64(c.winner, kNone64, 2 * (size_t)c.n - 4);  // once per build: a round consumes (resets) the winners it used
   memset(st, 0, sizeof *st);
   int zero[15] = {0}, host[8];
   int* list[2] = {listA, listB};
@@ -268,14 +266,15 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
     // the voters: this level, and with leftovers all levels before it (inserted points leave at once)
     const int lo = carry > 0 ? 0 : L;
     c.plist = lvl_order + lvl_off[lo];
-    c.plist_off = lvl_off[lo];
     m = lvl_off[L + 1] - lvl_off[lo];
     c.n_plist = m;
     remaining += carry;
     for (int rounds_here = 0; remaining > 0 && (L == K || rounds_here < kRoundsPerLevel); rounds_here++) {
       st->rounds++;
       be.locate_round(c, m);
-      // ONE readback per round: the number of triangles that received a vote (= splits) and the error bits
+      be.template launch<KSplitFlag>(c, c.n_tri);   // flags for the scan + the winner list
+      be.exclusive_scan_async(c.rank, c.n_tri);
+      // ONE readback per round: the error bits and the number of splits (= length of the winner list)
       be.read_ints(host, c.counters + FM_C_ERR, 2);
       static_assert(FM_C_NWIN == FM_C_ERR + 1, "one readback for both");
       const int nsplit = host[1];
@@ -292,7 +291,9 @@ int dt_run(B& be, DtCtx& c, int* listA, int* listB, const int* lvl_order, const 
       c.qcount = c.counters;
       // the splits run over the winner list; its length is on the device, the host knows it too by now
       be.template launch_counted<KSplit>(c, FM_C_NWIN, nsplit);
-      be.template launch_counted<KWinnerReset>(c, FM_C_NWIN, nsplit);
+      // the winners are consumed: all ones again, through the list when the round was small
+      if ((long long)nsplit * 16 < c.n_tri) be.template launch_counted<KWinnerReset>(c, FM_C_NWIN, nsplit);
+      else be.fill64(c.winner, kNone64, (size_t)c.n_tri);
       {
         int zero1 = 0;
         be.write_ints(c.counters + FM_C_NWIN, &zero1, 1);

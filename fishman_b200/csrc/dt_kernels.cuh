@@ -18,6 +18,9 @@
 // source runs (a) as the CUDA kernels of the product library and (b) thread by
 // thread on the host in tests/emu (CPU logic tests only; never shipped).
 #pragma once
+#if defined(__CUDACC__)
+#include <cooperative_groups.h>
+#endif
 #include "predicates.cuh"
 
 namespace fm {
@@ -46,6 +49,23 @@ inline T fm_host_exch(T* p, T v) { T o = *p; *p = v; return o; }
 #define FM_ATOMIC_EXCH32(p, v) fm_host_exch<int>((int*)(p), (int)(v))
 #endif
 
+// counter++ returning the old value, for the list heads every thread of a launch may bump
+// (queue lengths, winner / flip / deferred lists).  On the device the lanes of a warp that arrive
+// together send ONE atomic to L2 and share the result (all those counters sit in one cache line:
+// a million first votes of an insertion round were a million serialised atomics on one address
+// and took longer than the walks that cast them).
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ int fm_count_inc(int* ctr) {
+  cooperative_groups::coalesced_group g = cooperative_groups::coalesced_threads();
+  int base = 0;
+  if (g.thread_rank() == 0) base = atomicAdd(ctr, (int)g.size());
+  return g.shfl(base, 0) + (int)g.thread_rank();
+}
+#define FM_COUNT_INC(p) fm_count_inc((int*)(p))
+#else
+#define FM_COUNT_INC(p) fm_host_add<int>((int*)(p), 1)
+#endif
+
 // One triangle slot: vertex ids and adjacency side by side, 32 bytes = one sector and one
 // 256-bit load for the passes that need both (all of them but the ring walk).
 struct alignas(32) Row {
@@ -64,8 +84,7 @@ enum {
   FM_C_MAXDISP = 10,   // 64-bit word: bits of the largest chord displacement ([10], [11])
   FM_C_ERR = 12,       // error bits (DtCtx::err points here in the CUDA library)
   FM_C_REQ = 13,       // sharded sweep: flip requests this rank found
-  FM_C_NWIN = 13,      // cold build (no sharded sweep runs then): triangles that received a first vote this
-                       // round = entries of DtCtx::wlist = splits of the round
+  FM_C_NWIN = 13,      // cold build (no sharded sweep runs then): entries of DtCtx::wlist = splits of the round
   FM_C_BND = 14,       // sharded sweep: swept triangles with a vertex owned by another rank
   FM_C_STAMP = 15,     // next unused stamp
   // [16..31]: state of a BATCH of warm Lloyd iterations queued without a host round trip
@@ -105,20 +124,16 @@ struct DtCtx {
   const int* plist;            // points taking part in this round (the current insertion level), or
                                // null = all points; thread i of the locate kernels handles plist[i]
   int n_plist;
-  const int* lvl_order;        // all points sorted by (level, internal index); plist = lvl_order + plist_off
-  int plist_off;
-  int boot_pos[4];             // positions of the four bootstrap points in lvl_order
-  int* wlist;                  // triangles that received their first vote this round (length counters[FM_C_NWIN])
+  int* wlist;                  // the triangles that split this round (KSplitFlag; length counters[FM_C_NWIN])
   int locate_only;             // sharded point location: walk and record loc[], the votes are cast later (KVote)
   const int* prev;             // per point: nearest point to the left (internal order) of a coarser level
   const int* next_rev;         // the same to the right, stored reversed: next_rev[n-1-i] = n-1-j for the
                                // smallest j >= i of a coarser level, or -1 (null = left side only)
   int level_thr;               // coarseness of the current level
   int level_max;               // coarsest class K
-  u64* winner;                 // per triangle: min over its points of (priority << 32 | position of the point in
-                               // lvl_order); all ones between rounds
-  int* rank;                   // scratch of 2n-3 ints (the winner list lives here)
-  int n_tri;                   // triangles alive (host bookkeeping; the final count is 2n-4)
+  u64* winner;                 // per triangle: min over its points of (priority << 32 | point); all ones between rounds
+  int* rank;                   // per triangle: exclusive scan of "splits this round"
+  int n_tri;                   // triangles alive at the start of the round
   // flip rounds
   int stamp;                   // global sub-round counter (>= 1)
   const int* stamp_dev;        // when non-null the device-resident stamp (counters[FM_C_STAMP]) overrides
@@ -226,13 +241,13 @@ FM_HD inline u64 morton_key(double x, double y, double z) {
 }
 
 FM_HD inline void defer_item(const DtCtx& c, int item) {
-  int pos = FM_ATOMIC_ADD32(&c.counters[FM_C_SLOW], 1);
+  int pos = FM_COUNT_INC(&c.counters[FM_C_SLOW]);
   c.slow[pos] = item;
 }
 
 FM_HD inline void queue_active(const DtCtx& c, int t, int stamp) {
   if (FM_ATOMIC_EXCH32(&c.amark[t], stamp) != stamp) {
-    int pos = FM_ATOMIC_ADD32(c.qcount, 1);
+    int pos = FM_COUNT_INC(c.qcount);
     c.next_active[pos] = t;
   }
 }
@@ -298,15 +313,6 @@ struct KLevelInit {
 #if defined(FM_COUNT_STEPS) && !defined(__CUDACC__)
 static long long fm_walk_stats[3];  // triangles visited, walks, walks longer than 30 steps
 #endif
-// The vote of the point at position lp of lvl_order (original id qi) for triangle t.  The first
-// vote a triangle receives in a round puts it on the winner list: the split then runs over that
-// list instead of over all triangle slots.
-FM_HD inline void cast_vote(const DtCtx& c, int t, int qi, int lp) {
-  u64 key = ((u64)hash32((unsigned)qi) << 32) | (unsigned)lp;
-  u64 old = FM_ATOMIC_MIN64(&c.winner[t], key);
-  if (old == kNone64) c.wlist[FM_ATOMIC_ADD32(&c.counters[FM_C_NWIN], 1)] = t;
-}
-
 template <bool EXACT>
 struct KLocateVoteT {
   FM_HD static void run(const DtCtx& c, int i) {
@@ -341,7 +347,8 @@ struct KLocateVoteT {
     fm_walk_stats[0] += steps + 1; fm_walk_stats[1] += 1; fm_walk_stats[2] += steps > 30;
 #endif
     if (c.locate_only) return;
-    cast_vote(c, t, qi, c.plist_off + i);
+    u64 key = ((u64)hash32((unsigned)qi) << 32) | (unsigned)p;
+    FM_ATOMIC_MIN64(&c.winner[t], key);   // no result wanted: a fire-and-forget reduction
   }
 };
 typedef KLocateVoteT<true> KLocateVote;
@@ -353,7 +360,19 @@ struct KVote {
     int p = c.plist ? c.plist[i] : i;
     int t = c.loc[p];
     if (t < 0) return;
-    cast_vote(c, t, (int)c.pts[p].id, c.plist_off + i);
+    u64 key = ((u64)hash32((unsigned)c.pts[p].id) << 32) | (unsigned)p;
+    FM_ATOMIC_MIN64(&c.winner[t], key);
+  }
+};
+
+// One thread per triangle slot alive: 1 if it splits this round (input of the scan that numbers the
+// new slots), and the splitting ones go on the winner list -- the split itself then runs over
+// that list, not over all slots.
+struct KSplitFlag {
+  FM_HD static void run(const DtCtx& c, int t) {
+    const bool w = c.winner[t] != kNone64;
+    c.rank[t] = w ? 1 : 0;
+    if (w) c.wlist[FM_COUNT_INC(&c.counters[FM_C_NWIN])] = t;
   }
 };
 
@@ -361,37 +380,31 @@ struct KVote {
 // One thread per entry of the winner list: triangle t won the point p.  (a,b,c) becomes
 //   A = (a,b,p) in slot t,  B = (b,c,p) in slot s1,  C = (c,a,p) in slot s1+1,
 // the new vertex always last (as DV:977-982), so the edge inherited from the
-// parent is edge 2 of each child.  The two new slots belong to the POINT, not to the round:
-// s1 = 4 + 2 * (position of p in lvl_order, the bootstrap points not counted).  No scan over the
-// triangles, no count the host has to wait for, and a slot numbering that depends on nothing
-// but the input (the ranks of a sharded mesh hold slot-for-slot identical replicas).  A
+// parent is edge 2 of each child.  New slots are numbered by the rank of the parent among the
+// splitting slots (the scan of KSplitFlag's flags): dense -- the flip rounds that follow work on
+// one compact range of fresh slots -- and a function of the input alone, whatever order the
+// list was filled in (the ranks of a sharded mesh hold slot-for-slot identical replicas).  A
 // neighbour that splits in the same launch is not touched: where ITS child will be follows from
-// its winner alone.
+// its rank alone.
 struct KSplit {
-  FM_HD static int slot_of(const DtCtx& c, int lp) {
-    int before = (c.boot_pos[0] < lp) + (c.boot_pos[1] < lp) + (c.boot_pos[2] < lp) + (c.boot_pos[3] < lp);
-    return 4 + 2 * (lp - before);
-  }
-  FM_HD static int child_slot(const DtCtx& c, int n, u64 wn, int e) {
-    // slot of the child of (splitting) triangle n, won by wn, that inherits n's edge e
-    int s1 = slot_of(c, (int)(wn & 0xffffffffULL));
+  FM_HD static int child_slot(const DtCtx& c, int n, int e) {
+    // slot of the child of (splitting) triangle n that inherits n's edge e
+    int s1 = c.n_tri + 2 * c.rank[n];
     return e == 2 ? n : (e == 0 ? s1 : s1 + 1);
   }
   FM_HD static void run(const DtCtx& c, int i) {
     int t = c.wlist[i];
     u64 w = c.winner[t];
-    int lp = (int)(w & 0xffffffffULL);
-    int p = c.lvl_order[lp];
+    int p = (int)(w & 0xffffffffULL);
     Row r = c.row[t];
     I4 v = r.v, a = r.a;
-    int s1 = slot_of(c, lp), s2 = s1 + 1;
+    int s1 = c.n_tri + 2 * c.rank[t], s2 = s1 + 1;
     int childOf[3] = {s1, s2, t};  // parent edge k -> child slot
     int outer[3];
     for (int k = 0; k < 3; k++) {
       int ne = geti(a, k), n = ne >> 2, e = ne & 3;
-      u64 wn = c.winner[n];
-      if (wn != kNone64) {
-        outer[k] = enc(child_slot(c, n, wn, e), 2);
+      if (c.winner[n] != kNone64) {
+        outer[k] = enc(child_slot(c, n, e), 2);
       } else {
         outer[k] = ne;
         ((int*)&c.row[n].a)[e] = enc(childOf[k], 2);
@@ -406,7 +419,7 @@ struct KSplit {
     queue_active(c, t, c.stamp);
     queue_active(c, s1, c.stamp);
     queue_active(c, s2, c.stamp);
-    FM_ATOMIC_ADD32(&c.counters[4], 1);
+    FM_COUNT_INC(&c.counters[4]);
   }
 };
 // after the split: the winners of the round are consumed (all ones again)
@@ -477,7 +490,8 @@ struct KSweepImpl {
     const int t = slot(c, item);
     if (c.pf_dist > 0 && t + c.pf_dist < c.n_tri) asm volatile("prefetch.global.L2 [%0];" ::"l"(c.row + t + c.pf_dist));
     const Row r = c.row[t];
-    const int hv = ((volatile const int*)c.counters)[FM_T_HALT];
+    const int hv = c.counters[FM_T_HALT];   // plain load: written only between launches, and a volatile
+                                            // (L2) load of ONE word by five million threads is a hot spot
     if (hv != 0 && r.v.x >= 0) return;   // (the second term only ties the branch to the row load's issue slot)
     body(c, item, t, r);
   }
@@ -521,7 +535,7 @@ struct KSweepImpl {
     if (unsure) { defer_item(c, item); return; }
     if (so < 0) FM_ATOMIC_ADD32(&c.counters[3], 1);
     if (fe >= 0 && SHARDED) {
-      c.req[FM_ATOMIC_ADD32(&c.counters[FM_C_REQ], 1)] = (t << 2) | fe;
+      c.req[FM_COUNT_INC(&c.counters[FM_C_REQ])] = (t << 2) | fe;
     } else if (fe >= 0) {
       c.flip_edge[t] = fe;
       u64 key = vote_key(c.stamp, t);
@@ -538,7 +552,7 @@ struct KSweepImpl {
         int lo = v.x < v.y ? (v.x < v.z ? v.x : v.z) : (v.y < v.z ? v.y : v.z);
         int hi = v.x > v.y ? (v.x > v.z ? v.x : v.z) : (v.y > v.z ? v.y : v.z);
         if (lo < c.blk_begin || hi >= c.blk_end)  // a vertex lives on another rank
-          c.bnd[FM_ATOMIC_ADD32(&c.counters[FM_C_BND], 1)] = t;
+          c.bnd[FM_COUNT_INC(&c.counters[FM_C_BND])] = t;
       }
     }
   }
@@ -573,7 +587,7 @@ struct KMark {
       // Only a fraction of the queue flips (measured: 6 of 32 lanes in a late insertion round);
       // one thread per queue entry would run the flip's chain of dependent gathers in nearly
       // empty warps.  The winners go on a compact list instead.
-      c.fliplist[FM_ATOMIC_ADD32(&c.counters[FM_C_NFLIP], 1)] = t;
+      c.fliplist[FM_COUNT_INC(&c.counters[FM_C_NFLIP])] = t;
     } else {
       queue_active(c, t, c.stamp + 1);  // lost the vote: try again next sub-round
     }
@@ -643,7 +657,7 @@ struct KFlip {   // over fliplist[0 .. counters[FM_C_NFLIP])
     }
     queue_active(c, t, c.stamp + 1);
     queue_active(c, n, c.stamp + 1);
-    FM_ATOMIC_ADD32(&c.counters[2], 1);
+    FM_COUNT_INC(&c.counters[2]);
   }
 };
 

@@ -32,6 +32,7 @@ template <class K> struct KName { static const char* get() { return "kernel"; } 
 FM_KNAME(KLocateVote, "locate_exact")
 FM_KNAME(KLocateVoteT<false>, "locate_vote")
 FM_KNAME(KWinnerReset, "winner_reset")
+FM_KNAME(KSplitFlag, "split_flag")
 FM_KNAME(KVote, "vote")
 FM_KNAME(KLevelInit, "level_init")
 FM_KNAME(KSplit, "split13")
@@ -70,7 +71,7 @@ struct fm_handle {
   int *orig = nullptr, *inv = nullptr;
   int* ringc = nullptr;  // ring cache of the Lloyd kernel: 8 ints per vertex
   // insertion levels: points sorted by (level, internal index), level offsets (host), scratch
-  int *lvl_order = nullptr, *lvl_pos = nullptr, *prev = nullptr, *next_rev = nullptr;
+  int *lvl_order = nullptr, *prev = nullptr, *next_rev = nullptr;
   int lvl_K = 0;
   std::vector<int> lvl_off;
   // triangulation
@@ -262,6 +263,12 @@ struct CudaBackend {
   }
   void fill32(int* p, int v, size_t n) {
     h->note_cuda(cudaMemsetAsync(p, v & 0xff, n * sizeof(int), h->stream), "fill32");
+  }
+  void exclusive_scan_async(int* p, int n) {
+    h->prof_begin();
+    size_t bytes = h->cub_bytes;
+    h->note_cuda(cub::DeviceScan::ExclusiveSum(h->cub_tmp, bytes, p, p, n, h->stream), "scan");
+    h->prof_end("cub_scan", n);
   }
   void read_ints(int* dst, const int* src, int n) {
     h->note_cuda(cudaMemcpyAsync(h->pinned, src, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream),
@@ -467,7 +474,7 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
     A(cudaMalloc((void**)&h->ringc, 32 * (size_t)n));
     A(cudaMemsetAsync(h->ringc, 0xff, 32 * (size_t)n, h->stream));
   }
-  A(dalloc(&h->lvl_order, n)); A(dalloc(&h->lvl_pos, n)); A(dalloc(&h->prev, n)); A(dalloc(&h->next_rev, n));
+  A(dalloc(&h->lvl_order, n)); A(dalloc(&h->prev, n)); A(dalloc(&h->next_rev, n));
   A(dalloc(&h->rows, T));
   A(dalloc(&h->rankbuf, T + 1)); A(dalloc(&h->flip_edge, T));
   A(dalloc(&h->role, T)); A(dalloc(&h->amark, T)); A(dalloc(&h->listA, T)); A(dalloc(&h->listB, T)); A(dalloc(&h->fliplist, T / 2 + 1));
@@ -534,7 +541,6 @@ static int create_impl(int32_t n, const double* hx, const double* hy, const doub
     while ((1 << key_bits) <= K + 1) key_bits++;
     A(cub::DeviceRadixSort::SortPairs(h->cub_tmp, bytes, lk, lk2, i0, h->lvl_order, n, 0, key_bits, h->stream));
     fm_level_offsets<<<1, 32, 0, h->stream>>>(n, lk2, K, doff);
-    fm_invert_perm<<<nb, 256, 0, h->stream>>>(n, h->lvl_order, h->lvl_pos);
     A(cudaMemcpyAsync(h->lvl_off.data(), doff, sizeof(int) * (K + 2), cudaMemcpyDeviceToHost, h->stream));
     A(cudaStreamSynchronize(h->stream));
     h->n_launch += 3;
@@ -573,7 +579,7 @@ extern "C" void fm_destroy(fm_handle* h) {
     for (void* p : mptrs)
       if (p) cudaFree(p);
   }
-  void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->lvl_pos, h->prev, h->next_rev, h->rows, h->rankbuf, h->flip_edge,
+  void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->next_rev, h->rows, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->fliplist, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cclon, h->cclat,
                   h->deg, h->ring_tri, h->ring_nbr, h->ecount, h->de, h->ve_vvt, h->ve_vc, h->stage};
@@ -682,7 +688,7 @@ static int triangulate_cold(fm_handle* h) {
   fm_init_loc<<<(h->n + 255) / 256, 256, 0, h->stream>>>(h->n, h->loc, boot[0], boot[1], boot[2], boot[3]);
   h->n_launch++;
   DtStats st;
-  int rc = dt_run(be, c, h->listA, h->listB, h->lvl_order, h->lvl_pos, h->lvl_off.data(), h->lvl_K, h->prev, boot, &h->stamp, &st,
+  int rc = dt_run(be, c, h->listA, h->listB, h->lvl_order, h->lvl_off.data(), h->lvl_K, h->prev, boot, &h->stamp, &st,
                   h->errmsg, sizeof h->errmsg);
   if (h->cuda_failed || rc) return 1;
   h->n_tri = c.n_tri;

@@ -26,12 +26,17 @@ __device__ __forceinline__ void use_device_stamp(VdCtx&) {}
 // while the row is in flight (KSweepImpl::run_gated), and the kernels of a cold build, which
 // never run in a halted batch, are not gated at all.
 __device__ __forceinline__ bool fm_halted(const int* counters) {
-  return counters && ((volatile const int*)counters)[FM_T_HALT] != 0;
+  return counters && counters[FM_T_HALT] != 0;   // written only between launches: a plain, L1-cacheable load
 }
 __device__ __forceinline__ bool fm_halted(const DtCtx& c) { return fm_halted(c.counters); }
 __device__ __forceinline__ bool fm_halted(const VdCtx& c) { return fm_halted(c.counters); }
 template <class K> struct KGated { static const bool value = false; };
-template <> struct KGated<KSweepT<false>> { static const bool value = true; };
+// The sharded sweep is gated (its request / boundary lists are not deduplicated and would grow
+// with every halted iteration).  The unsharded sweep is NOT: even overlapped with the row load the
+// gate cost it 7 of 122 us (A/B on one box, profiles/r02_g_ab_warm.txt), and a sweep in a halted
+// batch is harmless -- it refreshes circumcentres and queues violated edges that fm_flip_coop,
+// which is gated, then drops (advancing the stamp, so that the marks it leaves are never taken
+// for those of a later repair).
 template <> struct KGated<KSweepShT<false>> { static const bool value = true; };
 
 // Resident 256-thread blocks per SM the launcher asks ptxas to make room for.  The gather
@@ -64,8 +69,7 @@ __global__ void __launch_bounds__(256) fm_kernel_counted(DtCtx c, int idx) {
 // the count is only known on the device).
 template <class K>
 __global__ void __launch_bounds__(128) fm_kernel_deferred(DtCtx c) {
-  if (fm_halted(c)) return;
-  use_device_stamp(c);
+  use_device_stamp(c);   // not gated: in a halted batch it still has to empty the deferred list of the (ungated) sweep
   int m = c.counters[FM_C_SLOW];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) K::run(c, c.slow[i]);
   // the last block to finish empties the list for the next filtered launch
@@ -86,7 +90,12 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
   int* list[2] = {listA, listB};
   volatile int* vc = c.counters;
   int stamp = vc[FM_C_STAMP];
-  if (fm_halted(c)) return;
+  if (fm_halted(c)) {
+    // Halted batch: the sweep before this launch still ran (it is not gated).  Drop what it queued
+    // and move to a fresh stamp: its amark / vote words must not pass for those of a later repair.
+    if (gid == 0) { vc[0] = 0; vc[1] = 0; vc[3] = 0; vc[FM_C_STAMP] = stamp + 1; }
+    return;
+  }
   if (vc[3] > 0) {  // a triangle turned over: leave everything to the rebuild (and stop the batch: the
                     // centroid stage tests the one halt word)
     if (gid == 0) vc[FM_T_HALT] = FM_HALT_REBUILD;
@@ -172,7 +181,7 @@ __global__ void fm_subround_end(int* counters, int cur, int nact) {
 template <bool UNIFORM>
 __global__ void __launch_bounds__(128, UNIFORM ? FM_OCC_CENTROID : FM_OCC_CENTROID_RHO) fm_centroid_update(const VdCtx c, int n) {
   extern __shared__ int ring_smem[];
-  if (c.abort_flag && *(volatile const int*)c.abort_flag) return;  // = the halt word (launch_centroid_kernel)
+  if (c.abort_flag && *c.abort_flag) return;  // = the halt word (launch_centroid_kernel)
   int j = blockIdx.x * blockDim.x + threadIdx.x;
   double disp = 0.0;
   if (j < n) disp = KCentroid::compute<UNIFORM>(c, c.cell_begin + j, ring_smem + threadIdx.x, blockDim.x);
@@ -391,10 +400,6 @@ __global__ void fm_level_offsets(int n, const unsigned* sorted_key, int K, int* 
     if (sorted_key[mid] < (unsigned)L) lo = mid + 1; else hi = mid;
   }
   off[L] = lo;
-}
-__global__ void fm_invert_perm(int n, const int* order, int* pos) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) pos[order[i]] = i;
 }
 __global__ void fm_prev_keys(int n, const P4* pts, int K, int thr, int* prev, int* next_rev) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;

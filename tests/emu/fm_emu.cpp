@@ -49,6 +49,10 @@ struct HostBackend {
   }
   void fill64(u64* p, u64 v, size_t n) { std::fill(p, p + n, v); }
   void fill32(int* p, int v, size_t n) { std::fill(p, p + n, v); }
+  void exclusive_scan_async(int* p, int n) {
+    int acc = 0;
+    for (int i = 0; i < n; i++) { int v = p[i]; p[i] = acc; acc += v; }
+  }
   void read_ints(int* dst, const int* src, int n) { memcpy(dst, src, sizeof(int) * n); }
   void write_ints(int* dst, const int* src, int n) { memcpy(dst, src, sizeof(int) * n); }
   int argmax_dot(const DtCtx& c, const double* d) {
@@ -140,15 +144,14 @@ struct EmuMesh {
     if (dt_bootstrap(be, c, boot, g_err, sizeof g_err)) return 1;
     for (int k = 0; k < 4; k++) loc[boot[k]] = -1;
     int K = dt_level_count(n);
-    std::vector<int> order(n), off(K + 2, 0), prev(n), pos(n);
+    std::vector<int> order(n), off(K + 2, 0), prev(n);
     std::iota(order.begin(), order.end(), 0);
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
       return point_class(pts[a].id, K) > point_class(pts[b].id, K);  // level = K - class, ascending
     });
-    for (int i = 0; i < n; i++) pos[order[i]] = i;
     for (int i = 0; i < n; i++) off[K - point_class(pts[i].id, K) + 1]++;
     for (int L = 0; L <= K; L++) off[L + 1] += off[L];
-    if (dt_run(be, c, listA.data(), listB.data(), order.data(), pos.data(), off.data(), K, prev.data(), boot, &stamp, &st,
+    if (dt_run(be, c, listA.data(), listB.data(), order.data(), off.data(), K, prev.data(), boot, &stamp, &st,
                g_err, sizeof g_err))
       return 1;
     if (c.n_tri != T) { snprintf(g_err, sizeof g_err, "triangle count %d != 2n-4", c.n_tri); return 1; }

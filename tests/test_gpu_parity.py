@@ -314,7 +314,19 @@ def test_lloyd_batches_equal_single_steps(fb):
     k = next(i for i, v in enumerate(more) if v <= tol) + 1
     it, md = b.lloyd(max_iter=100, tol=tol, warm=True)
     assert it == k and md == more[k - 1]
-    a.close(); b.close()
+    # the launches of the batch after the one that converged did nothing lasting: the mesh is in the
+    # state the single-step loop reaches after k steps, and the next repair starts on clean marks
+    c = fb.Mesh.from_xyz(p)
+    c.lloyd(max_iter=12 + k, warm=True)
+    assert np.array_equal(b.generators(), c.generators())
+    b.retriangulate(warm=True)
+    fresh = fb.Mesh.from_xyz(b.generators())
+    fresh.delaunay_triangulation()
+    assert np.array_equal(_check.canonical(b.triangles()[0]), _check.canonical(fresh.triangles()[0]))
+    it2, md2 = b.lloyd(max_iter=3, warm=True)
+    c.lloyd(max_iter=3, warm=True)
+    assert it2 == 3 and np.array_equal(b.generators(), c.generators())
+    a.close(); b.close(); c.close(); fresh.close()
 
 
 @pytest.mark.parametrize("n", [40, 200, 2000, 20000])
