@@ -1054,7 +1054,7 @@ static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool gua
     cnt = h->n;
   }
   if (cnt <= 0) return;
-  const int B = 128;
+  const int B = d.kind == 0 ? FM_CENTROID_BLOCK : FM_CENTROID_BLOCK_RHO;
   size_t smem = sizeof(int) * kRingCap * B;
   h->prof_begin();
   if (d.kind == 0) fm_centroid_update<true><<<(cnt + B - 1) / B, B, smem, h->stream>>>(c, cnt);

@@ -172,27 +172,43 @@ __global__ void fm_subround_end(int* counters, int cur, int nact) {
 // ring triangle ids are staged in shared memory, the per-cell chord displacement is reduced
 // with warp shuffles, then once per block through shared memory, and one atomicMax per block
 // reaches HBM.
-#ifndef FM_OCC_CENTROID
-#define FM_OCC_CENTROID 8
+// No block-level reduction: the warps of a block used to meet at a barrier for the shared-memory
+// maximum (ncu: stall_barrier 1.2 per issue) -- now every warp sends its own maximum, if it beats
+// the one seen so far.  Worth 1 % (uniform) / 2.6 % (x4); the block size itself (32 / 64 / 128
+// threads) measures the same (profiles/r02_i_ab_centroid_block.txt).
+#ifndef FM_CENTROID_BLOCK
+#define FM_CENTROID_BLOCK 64
 #endif
-#ifndef FM_OCC_CENTROID_RHO
-#define FM_OCC_CENTROID_RHO 4   // with a density: seven evaluations in flight per sub-triangle want ~128 registers
+#ifndef FM_CENTROID_BLOCK_RHO
+#define FM_CENTROID_BLOCK_RHO 64   // with a density: seven evaluations in flight per sub-triangle want ~128 registers
+#endif
+#ifndef FM_CENTROID_WARPS
+#define FM_CENTROID_WARPS 32       // resident warps per SM the register budget is set for (uniform): 64 registers
+#endif
+#ifndef FM_CENTROID_WARPS_RHO
+#define FM_CENTROID_WARPS_RHO 16   // 128 registers
 #endif
 template <bool UNIFORM>
-__global__ void __launch_bounds__(128, UNIFORM ? FM_OCC_CENTROID : FM_OCC_CENTROID_RHO) fm_centroid_update(const VdCtx c, int n) {
+__global__ void __launch_bounds__(UNIFORM ? FM_CENTROID_BLOCK : FM_CENTROID_BLOCK_RHO,
+                                  UNIFORM ? FM_CENTROID_WARPS * 32 / FM_CENTROID_BLOCK : FM_CENTROID_WARPS_RHO * 32 / FM_CENTROID_BLOCK_RHO)
+    fm_centroid_update(const VdCtx c, int n) {
   extern __shared__ int ring_smem[];
-  if (c.abort_flag && *c.abort_flag) return;  // = the halt word (launch_centroid_kernel)
   int j = blockIdx.x * blockDim.x + threadIdx.x;
+  // the two records every cell starts from are requested before the halt word is looked at
+  // (a gate in front of the first load is a whole memory latency per warp)
+  if (j < n) {
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pts + c.cell_begin + j));
+    if (c.ringc) asm volatile("prefetch.global.L1 [%0];" ::"l"(c.ringc + 8 * (size_t)(c.cell_begin + j)));
+  }
+  if (c.abort_flag && *c.abort_flag) return;  // = the halt word (launch_centroid_kernel)
   double disp = 0.0;
   if (j < n) disp = KCentroid::compute<UNIFORM>(c, c.cell_begin + j, ring_smem + threadIdx.x, blockDim.x);
   for (int o = 16; o > 0; o >>= 1) disp = fmax(disp, __shfl_xor_sync(0xffffffffu, disp, o));
-  __shared__ double wmax[4];
-  if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = disp;
-  __syncthreads();
-  if (threadIdx.x < 32) {
-    double v = (threadIdx.x < (blockDim.x >> 5)) ? wmax[threadIdx.x] : 0.0;
-    for (int o = 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
-    if (threadIdx.x == 0 && v > 0.0) atomicMax(c.maxdisp, (u64)__double_as_longlong(v));
+  // one atomicMax per WARP at most: only a warp that beats the maximum seen so far sends one
+  // (the word is read first; after the first few warps almost nobody does)
+  if ((threadIdx.x & 31) == 0 && disp > 0.0) {
+    const u64 bits = (u64)__double_as_longlong(disp);
+    if (bits > *(volatile u64*)c.maxdisp) atomicMax(c.maxdisp, bits);
   }
 }
 

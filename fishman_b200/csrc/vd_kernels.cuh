@@ -383,6 +383,10 @@ struct KCentroid {
         rec[1] = I4{q[4], q[5], q[6], q[7]};
       }
     }
+    // (Tried: prefetch.global.L1 / .L2 of ALL ring circumcentres right here, because a fifth of the
+    // stall samples wait for the loop's one-trip-ahead loads.  Slower: 0.180 against 0.173 ms -- the
+    // extra address arithmetic and cache pressure cost more than the latency hidden;
+    // profiles/r02_i_ab_centroid_prefetch.txt.)
     double M0 = 0.0, M1 = 0.0, M2 = 0.0;
     const double gg = g.x * g.x + g.y * g.y + g.z * g.z;
     if (UNIFORM && d <= kRingCap) {
