@@ -754,13 +754,12 @@ static int repair_async(fm_handle* h, bool sharded = false, bool in_batch = fals
   cs.req = f.inbox[h->rank];  // this rank's own region of its own inbox
   cs.bnd = h->bnd;
   f.row = h->rows; f.req = cs.req; f.bnd = h->bnd; f.counters = h->counters;
-  f.rank = h->rank; f.size = h->size;
+  f.rank = h->rank; f.size = h->size; f.pc = h->peer_ctx;
   be.launch_filtered<KSweepShT>(cs, h->sweep_end - h->sweep_begin);
   h->prof_begin();
-  fm_sweep_fanout<<<h->sms, 256, 0, h->stream>>>(f);
+  fm_sweep_fanout<<<h->sms, 256, 0, h->stream>>>(f);   // + the barrier, in the tail of its last block
   h->note_cuda(cudaGetLastError(), "sweep_fanout");
   h->prof_end("sweep_fanout", 0);
-  launch_peer_barrier(h, 2);
   h->prof_begin();
   fm_apply_requests<<<h->sms * 2, 256, 0, h->stream>>>(c, h->peer_ctx, h->inbox, h->inbox_cap);
   h->note_cuda(cudaGetLastError(), "apply_requests");
@@ -1036,10 +1035,10 @@ static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool gua
 // Centroid stage of one iteration.  On a sharded mesh with attached peers the kernel runs
 // between two barriers: no rank overwrites generators another rank is still reading, and the
 // iteration ends when every block has arrived everywhere.
-static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded) {
+static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded, bool closing_barrier = true) {
   if (h->peers_attached) launch_peer_barrier(h, 0);
   launch_centroid_kernel(h, rho, guarded);
-  if (h->peers_attached) launch_peer_barrier(h, 1);
+  if (h->peers_attached && closing_barrier) launch_peer_barrier(h, 1);
 }
 
 static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded, bool dry) {
@@ -1073,7 +1072,8 @@ static bool same_density(const fm_density* a, const fm_density& b) {
 
 static void launch_iter_end(fm_handle* h) {
   h->prof_begin();
-  fm_iter_end<<<1, 1, 0, h->stream>>>(h->counters);
+  if (h->peers_attached) fm_iter_end_peers<<<1, 32, 0, h->stream>>>(h->peer_ctx, h->counters);  // + the closing barrier
+  else fm_iter_end<<<1, 1, 0, h->stream>>>(h->counters);
   h->note_cuda(cudaGetLastError(), "iter_end");
   h->prof_end("iter_end", 0);
 }
@@ -1084,7 +1084,7 @@ static void launch_iter_end(fm_handle* h) {
 // size in it is fixed for the life of the handle, the stamp and the queue lengths live on the
 // device.  If capture is not possible the launches are issued directly.
 static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
-  const int launches = h->peers_attached ? 10 : 5;  // sweep, deferred sweep, flip loop, centroid, iter_end (+ fan-out, 3 barriers, apply)
+  const int launches = h->peers_attached ? 8 : 5;  // sweep, deferred sweep, flip loop, centroid, iter_end (+ fan-out, 1 barrier, apply)
   if (!h->profile && !h->graph_disabled) {
     if (h->warm_graph && !same_density(rho, h->warm_graph_rho)) {
       cudaGraphExecDestroy(h->warm_graph);
@@ -1097,7 +1097,7 @@ static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
       bool ok = (e == cudaSuccess);
       if (ok) {
         int rc = repair_async(h, h->peers_attached, true);
-        launch_centroid(h, rho, true);
+        launch_centroid(h, rho, true, false);
         launch_iter_end(h);
         e = cudaStreamEndCapture(h->stream, &g);
         ok = (rc == 0 && e == cudaSuccess && g != nullptr && !h->cuda_failed);
@@ -1126,7 +1126,7 @@ static int warm_iteration_enqueue(fm_handle* h, const fm_density* rho) {
     }
   }
   if (repair_async(h, h->peers_attached, true)) return 1;
-  launch_centroid(h, rho, true);
+  launch_centroid(h, rho, true, false);
   launch_iter_end(h);
   return 0;
 }

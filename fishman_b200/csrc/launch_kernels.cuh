@@ -144,7 +144,7 @@ __global__ void fm_bump_stamp(int* counters, int by) { counters[FM_C_STAMP] += b
 // back -- the convergence test (north-star kernel (d): the displacement maximum is already
 // reduced), the "a triangle turned over, rebuild" decision, the statistics -- and the reset of
 // the per-iteration counters for the next iteration of the batch.
-__global__ void fm_iter_end(int* counters) {
+__device__ __forceinline__ void fm_iter_end_body(int* counters) {
   if (counters[FM_T_HALT]) return;
   if (counters[FM_C_ERR]) { counters[FM_T_HALT] = FM_HALT_ERROR; return; }   // counters kept for the report
   if (counters[3] > 0) { counters[FM_T_HALT] = FM_HALT_REBUILD; return; }    // the centroid kernel did nothing
@@ -158,6 +158,7 @@ __global__ void fm_iter_end(int* counters) {
 #pragma unroll
   for (int k = 0; k < 15; k++) counters[k] = 0;
 }
+__global__ void fm_iter_end(int* counters) { fm_iter_end_body(counters); }
 
 // bookkeeping at the end of a host-driven flip sub-round (what thread 0 of fm_flip_coop does)
 __global__ void fm_subround_end(int* counters, int cur, int nact) {
@@ -239,17 +240,16 @@ struct PeerCtx {
 // requests and circumcentres have landed here, and their counts are known); phase 3 is a plain
 // barrier (sharded point location).  One warp; lane k talks to rank k.  A rank that does
 // not show up within ~2 s of SM clocks sets FM_E_PEER instead of hanging the device.
-__global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
+__device__ __forceinline__ void fm_peer_barrier_body(const PeerCtx& pc, int phase, int* counters) {
   __shared__ int ep;
   const int k = threadIdx.x;
-  if (fm_halted(counters)) return;  // every rank takes the same decision (combined counts / maxima), or it is an error path
   PeerSync* self = pc.sync[pc.rank];
   if (k == 0) {
     ep = self->epoch + 1;
     self->epoch = ep;
     if (phase == 0) self->maxdisp_all = 0;
   }
-  __syncthreads();
+  __syncwarp();
   const int e = ep;
   if (k < pc.size) {
     if (phase == 1) {
@@ -271,11 +271,25 @@ __global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
       }
     }
   }
-  __syncthreads();
+  __syncwarp();
   if (phase == 1 && k == 0) {
     __threadfence_system();
     *(volatile u64*)(counters + FM_C_MAXDISP) = *(volatile u64*)&self->maxdisp_all;
   }
+}
+__global__ void fm_peer_barrier(PeerCtx pc, int phase, int* counters) {
+  if (fm_halted(counters)) return;  // every rank takes the same decision (combined counts / maxima), or it is an error path
+  fm_peer_barrier_body(pc, phase, counters);
+}
+
+// Sharded mesh: the barrier that closes the centroid stage (phase 1: all ranks' generator stores have
+// landed here, the displacement maxima are combined) and fm_iter_end in ONE launch of one warp.
+__device__ __forceinline__ void fm_iter_end_body(int* counters);
+__global__ void fm_iter_end_peers(PeerCtx pc, int* counters) {
+  if (fm_halted(counters)) return;
+  fm_peer_barrier_body(pc, 1, counters);
+  __syncwarp();
+  if (threadIdx.x == 0) fm_iter_end_body(counters);
 }
 
 // Sharded point location: the slots this rank's walks ended in, to every rank's loc[]
@@ -300,11 +314,13 @@ struct FanCtx {
   P4* cc[8];       // by rank: circumcentre arrays
   const Row* row;
   const int *req, *bnd;
-  const int* counters;
+  int* counters;
   int rank, size, blk_per;
+  PeerCtx pc;      // the barrier that follows the fan-out runs in the tail of this kernel
 };
 __global__ void __launch_bounds__(256) fm_sweep_fanout(FanCtx f) {
   if (fm_halted(f.counters)) return;
+  __shared__ int last_block;
   const int gsz = gridDim.x * blockDim.x, gid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nreq = f.counters[FM_C_REQ], nbnd = f.counters[FM_C_BND];
   for (int i = gid; i < nreq; i += gsz) {
@@ -321,6 +337,16 @@ __global__ void __launch_bounds__(256) fm_sweep_fanout(FanCtx f) {
     if (o1 != f.rank && o1 != o0) f.cc[o1][t] = rec;
     if (o2 != f.rank && o2 != o0 && o2 != o1) f.cc[o2][t] = rec;
   }
+  // The block that finishes last runs the barrier (phase 2: requests and circumcentres have landed
+  // everywhere, their counts are known) -- one launch and one launch gap fewer per iteration.
+  __threadfence_system();   // this block's peer stores are out before it counts itself done
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    last_block = atomicAdd(f.counters + FM_C_SLOWDONE, 1) == (int)gridDim.x - 1;   // (idle between filtered launches)
+    if (last_block) f.counters[FM_C_SLOWDONE] = 0;
+  }
+  __syncthreads();
+  if (last_block && threadIdx.x < 32) fm_peer_barrier_body(f.pc, 2, f.counters);
 }
 
 // After a sharded sweep and its barrier: every rank turns ALL requests (its own and its peers')

@@ -75,7 +75,9 @@ def main():
     c.set_generators_block_soa(pb[0].copy(), pb[1].copy(), pb[2].copy())     # every rank re-uploads its block of the START set
     block_set_ok = np.array_equal(c.generators(), p)
     it_c, md_c = c.lloyd(rho, max_iter=iters, tol=0.0, warm=True)
-    block_set_ok = block_set_ok and np.array_equal(c.generators(), g_ref)
+    # same trajectory, but not bit for bit: the connectivity was REPAIRED back to that of p (other slot
+    # numbers than a fresh build, and a cell's quadrature sum starts at its lowest-numbered triangle)
+    block_set_ok = block_set_ok and np.abs(c.generators() - g_ref).max() < 1e-13
     all_ids = [None] * world
     dist.all_gather_object(all_ids, ids.tolist())
     cover_ok = sorted(v for part in all_ids for v in part) == list(range(1, n + 1))
