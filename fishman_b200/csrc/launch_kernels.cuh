@@ -43,8 +43,11 @@ template <> struct KGated<KSweepShT<false>> { static const bool value = true; };
 // kernels are latency / L1 bound; their filter-only forms (K<false>) contain no calls and
 // fit 64 registers without spilling, so four blocks hide the gather latency.
 template <class K> struct KOcc { static const int value = 1; };
-template <> struct KOcc<KSweepT<false>> { static const int value = 4; };
-template <> struct KOcc<KSweepShT<false>> { static const int value = 4; };
+#ifndef FM_OCC_SWEEP
+#define FM_OCC_SWEEP 4
+#endif
+template <> struct KOcc<KSweepT<false>> { static const int value = FM_OCC_SWEEP; };
+template <> struct KOcc<KSweepShT<false>> { static const int value = FM_OCC_SWEEP; };
 template <> struct KOcc<KLocateVoteT<false>> { static const int value = 4; };
 template <> struct KOcc<KCheckT<false>> { static const int value = 4; };
 

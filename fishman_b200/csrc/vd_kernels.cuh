@@ -227,21 +227,6 @@ FM_HD inline double density_node(const Density& r, double qx, double qy, double 
 #define FM_QW1 0.12593918054482715260
 #define FM_QW2 0.13239415278850618074
 
-// 1/sqrt(v) for v of order 1: hardware seed (MUFU.RSQ64H, ~2^-22) + ONE cubically convergent
-// step  y (1 + e/2 + 3 e^2/8),  e = 1 - v y^2  = 5 DFMA-class instructions instead of the ~20
-// of the library call; the remaining relative error (~0.3 e^3) is far below 2^-53.
-FM_HD inline double fm_rsqrt(double v) {
-#if defined(__CUDA_ARCH__)
-  double y;
-  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
-  double e = fma(-(v * y), y, 1.0);
-  double p = fma(0.375, e, 0.5);
-  return fma(y, p * e, y);
-#else
-  return 1.0 / sqrt(v);
-#endif
-}
-
 // Quadrature of one sub-triangle (g, a, b) added to the moment M.  The seven nodes are
 // S/3 and (A S + (B - A) v) for v in {g, a, b}, (A, B) in {(A1, B1), (A2, B2)}, S = g + a + b.
 // Only q/|q| enters, so each node is taken as q = S + kappa v (kappa = (B - A)/A) and
@@ -432,16 +417,27 @@ struct KCentroid {
         aa = bb;
       }
     }
-    double nrm = sqrt(M0 * M0 + M1 * M1 + M2 * M2);
-    if (!(nrm > 0.0)) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
+    const double mm = M0 * M0 + M1 * M1 + M2 * M2;
+    if (!(mm > 0.0)) { *c.err |= FM_E_TOPOLOGY; return 0.0; }
+#if defined(__CUDA_ARCH__) && !defined(FM_CENTROID_DIVIDE)
+    const double rn = fm_rsqrt(mm);   // projection to the sphere: three products instead of sqrt + three divisions
+    double n0 = M0 * rn, n1 = M1 * rn, n2 = M2 * rn;
+#else
+    const double nrm = sqrt(mm);
     double n0 = M0 / nrm, n1 = M1 / nrm, n2 = M2 / nrm;
+#endif
     double dx = n0 - g.x, dy = n1 - g.y, dz = n2 - g.z;
     if (!c.dry) {
       const P4 moved{n0, n1, n2, gq.id};  // whole 32-byte records: one store, one full sector / NVLink packet
       c.pts[i] = moved;
       for (int q = 0; q < c.n_peers; q++) c.peer_pts[q][i] = moved;
     }
-    return sqrt(dx * dx + dy * dy + dz * dz);
+    const double d2 = dx * dx + dy * dy + dz * dz;
+#if defined(__CUDA_ARCH__) && !defined(FM_CENTROID_DIVIDE)
+    return d2 > 0.0 ? d2 * fm_rsqrt(d2) : 0.0;
+#else
+    return sqrt(d2);
+#endif
   }
   FM_HD static void run(const VdCtx& c, int j) {  // generic form (host tests)
     int ring[kRingCap];
