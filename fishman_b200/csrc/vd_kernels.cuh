@@ -227,6 +227,24 @@ FM_HD inline double density_node(const Density& r, double qx, double qy, double 
 #define FM_QW1 0.12593918054482715260
 #define FM_QW2 0.13239415278850618074
 
+// 1/sqrt for the weights of the uniform quadrature: the hardware seed + ONE Newton step, 4 fp64
+// instructions instead of fm_rsqrt's 5 (8 of the 117 per sub-triangle; centroid kernel 0.168 ->
+// 0.162 ms).  Relative error 1.5 e^2 ~ 1e-13 with the seed's e ~ 2^-22: a weight error of that size
+// moves a centroid by at most that fraction of the CELL DIAMETER, i.e. < 2e-13 on any mesh of the
+// unit sphere and ~1e-16 at 2.6M generators -- inside the 1e-12 of the specification with room to
+// spare (parity tests unchanged: 1e-12 against the oracle, 1e-13 against the 50-digit fixtures).
+// -DFM_QUAD_CUBIC restores the cubic step.
+FM_HD inline double fm_rsqrt_q(double v) {
+#if defined(__CUDA_ARCH__) && !defined(FM_QUAD_CUBIC)
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(v));
+  double e = __fma_rn(-__dmul_rn(v, y), y, 1.0);
+  return __fma_rn(__dmul_rn(y, 0.5), e, y);
+#else
+  return fm_rsqrt(v);
+#endif
+}
+
 // Quadrature of one sub-triangle (g, a, b) added to the moment M.  The seven nodes are
 // S/3 and (A S + (B - A) v) for v in {g, a, b}, (A, B) in {(A1, B1), (A2, B2)}, S = g + a + b.
 // Only q/|q| enters, so each node is taken as q = S + kappa v (kappa = (B - A)/A) and
@@ -297,17 +315,17 @@ FM_HD inline void quad_uniform(const RingVertex& a, const RingVertex& b, double 
   const double k1 = (FM_QB1 - FM_QA1) / FM_QA1, k2 = (FM_QB2 - FM_QA2) / FM_QA2;
   double c0 = a.u.y * b.u.z - a.u.z * b.u.y, c1 = a.u.z * b.u.x - a.u.x * b.u.z, c2 = a.u.x * b.u.y - a.u.y * b.u.x;
   double n2 = c0 * c0 + c1 * c1 + c2 * c2;
-  double A = n2 > 0.0 ? 0.5 * n2 * fm_rsqrt(n2) : 0.0;
+  double A = n2 > 0.0 ? 0.5 * n2 * fm_rsqrt_q(n2) : 0.0;
   double ab = a.p.x * b.p.x + a.p.y * b.p.y + a.p.z * b.p.z;
   double Sg = gg + a.gp + b.gp, Sa = a.gp + a.pp + ab, Sb = b.gp + ab + b.pp;
   double SS = Sg + Sa + Sb;
-  double w0 = FM_QW0 * fm_rsqrt(SS);
-  double w1g = FM_QW1 * fm_rsqrt(fma(k1 * k1, gg, fma(2.0 * k1, Sg, SS)));
-  double w1a = FM_QW1 * fm_rsqrt(fma(k1 * k1, a.pp, fma(2.0 * k1, Sa, SS)));
-  double w1b = FM_QW1 * fm_rsqrt(fma(k1 * k1, b.pp, fma(2.0 * k1, Sb, SS)));
-  double w2g = FM_QW2 * fm_rsqrt(fma(k2 * k2, gg, fma(2.0 * k2, Sg, SS)));
-  double w2a = FM_QW2 * fm_rsqrt(fma(k2 * k2, a.pp, fma(2.0 * k2, Sa, SS)));
-  double w2b = FM_QW2 * fm_rsqrt(fma(k2 * k2, b.pp, fma(2.0 * k2, Sb, SS)));
+  double w0 = FM_QW0 * fm_rsqrt_q(SS);
+  double w1g = FM_QW1 * fm_rsqrt_q(fma(k1 * k1, gg, fma(2.0 * k1, Sg, SS)));
+  double w1a = FM_QW1 * fm_rsqrt_q(fma(k1 * k1, a.pp, fma(2.0 * k1, Sa, SS)));
+  double w1b = FM_QW1 * fm_rsqrt_q(fma(k1 * k1, b.pp, fma(2.0 * k1, Sb, SS)));
+  double w2g = FM_QW2 * fm_rsqrt_q(fma(k2 * k2, gg, fma(2.0 * k2, Sg, SS)));
+  double w2a = FM_QW2 * fm_rsqrt_q(fma(k2 * k2, a.pp, fma(2.0 * k2, Sa, SS)));
+  double w2b = FM_QW2 * fm_rsqrt_q(fma(k2 * k2, b.pp, fma(2.0 * k2, Sb, SS)));
   double cS = w0 + ((w1g + w1a) + w1b) + ((w2g + w2a) + w2b);
   double tg = A * (cS + fma(k1, w1g, k2 * w2g));
   double ta = A * (cS + fma(k1, w1a, k2 * w2a));
