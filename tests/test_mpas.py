@@ -195,4 +195,4 @@ def test_gen_mesh_end_to_end(tmp_path):
         assert np.abs(d[name] - r[name]).max() < TOL, name
     assert np.abs(np.stack([d["xEdge"], d["yEdge"], d["zEdge"]], 1) - r["xyzEdge"]).max() < TOL
     assert np.abs(np.stack([d["xCell"], d["yCell"], d["zCell"]], 1) - p).max() == 0.0
-    assert np.abs(np.abs(d["weightsOnEdge"]) - np.abs(r["weightsOnEdge"])).max() < 1e-9
+    assert np.abs(d["weightsOnEdge"] - r["weightsOnEdge"]).max() < 1e-9   # signed: a sign error must not pass
