@@ -89,8 +89,9 @@ def peaks():
 
 class ClockSampler:
     """Samples SM clock and throttle reasons through NVML from a thread while the timed
-    region runs (the ctypes calls into the library release the GIL).  ~1 ms period: the timed
-    region of a warm run is only tens of ms, far shorter than one nvidia-smi -lms tick."""
+    region runs (the ctypes calls into the library release the GIL).  Sub-millisecond period (an NVML
+    query itself takes 0.1-1 ms): the timed region of a warm run is only a few ms, far shorter than
+    one nvidia-smi -lms tick."""
 
     def __init__(self, index):
         self.index, self.rows, self.stop_flag, self.th, self.err = index, [], False, None, None
@@ -119,7 +120,7 @@ class ClockSampler:
             except Exception as e:  # noqa: BLE001
                 self.err = repr(e)
                 return
-            time.sleep(0.001)
+            time.sleep(0.0002)
 
     def start(self):
         if self.nv:
