@@ -471,6 +471,33 @@ struct KCheckT {
     int t = c.active[i];
     Row r = c.row[t];
     I4 v = r.v, a = r.a;
+#if !defined(FM_CHECK_SEQUENTIAL)
+    // All gathers of the three tests are requested before the first is consumed (as the sweep does):
+    // the three opposite-vertex ids together, then the six vertex records together -- two dependent
+    // levels after the row instead of up to six when each edge's chain waited for the test before it.
+    const int* trow = (const int*)c.row;
+    int d0 = trow[8 * (size_t)(a.x >> 2) + (a.x & 3)];
+    int d1 = trow[8 * (size_t)(a.y >> 2) + (a.y & 3)];
+    int d2 = trow[8 * (size_t)(a.z >> 2) + (a.z & 3)];
+    P4 qa = c.pts[v.x], qb = c.pts[v.y], qc = c.pts[v.z];
+    P4 q0 = c.pts[d0], q1 = c.pts[d1], q2 = c.pts[d2];
+    P3 pa{qa.x, qa.y, qa.z}, pb{qb.x, qb.y, qb.z}, pc{qc.x, qc.y, qc.z};
+    int ia = (int)qa.id, ib = (int)qb.id, ic = (int)qc.id;
+    int fe = -1;
+    int s = incircle_t<EXACT>(pa, pb, pc, P3{q0.x, q0.y, q0.z}, ia, ib, ic, (int)q0.id);
+    if (!EXACT && s == 0) { defer_item(c, i); return; }
+    if (s > 0) fe = 0;
+    if (fe < 0) {
+      s = incircle_t<EXACT>(pa, pb, pc, P3{q1.x, q1.y, q1.z}, ia, ib, ic, (int)q1.id);
+      if (!EXACT && s == 0) { defer_item(c, i); return; }
+      if (s > 0) fe = 1;
+    }
+    if (fe < 0) {
+      s = incircle_t<EXACT>(pa, pb, pc, P3{q2.x, q2.y, q2.z}, ia, ib, ic, (int)q2.id);
+      if (!EXACT && s == 0) { defer_item(c, i); return; }
+      if (s > 0) fe = 2;
+    }
+#else
     int ia, ib, ic, idd;
     P3 pa = ldv(c, v.x, ia), pb = ldv(c, v.y, ib), pc = ldv(c, v.z, ic);
     int fe = -1;
@@ -482,6 +509,7 @@ struct KCheckT {
       if (!EXACT && s == 0) { defer_item(c, i); return; }
       if (s > 0) { fe = k; break; }
     }
+#endif
     c.flip_edge[t] = fe;
     if (fe >= 0) {
       u64 key = vote_key(c.stamp, t);

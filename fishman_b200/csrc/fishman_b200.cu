@@ -345,7 +345,17 @@ struct CudaBackend {
       c.n_active = nact;
       c.next_active = list[cur ^ 1];
       c.qcount = c.counters + (cur ^ 1);
-      if (!skip_check) launch_filtered<KCheckT>(c, nact);
+      static const bool coop4 = getenv("FM_CHECK_COOP4") && atoi(getenv("FM_CHECK_COOP4")) != 0;
+      if (!skip_check && coop4) {  // A/B: four lanes per queued triangle, then the exact kernel over what was deferred
+        h->prof_begin();
+        fm_check_coop4<<<(unsigned)((4LL * nact + 255) / 256), 256, 0, h->stream>>>(c, nact);
+        h->note_cuda(cudaGetLastError(), "flip_check_coop4");
+        h->prof_end("flip_check_coop4", nact);
+        h->prof_begin();
+        fm_kernel_deferred<KCheckT<true>><<<h->sms * 4, 128, 0, h->stream>>>(c);
+        h->note_cuda(cudaGetLastError(), "check_exact");
+        h->prof_end("check_exact", 0);
+      } else if (!skip_check) launch_filtered<KCheckT>(c, nact);
       skip_check = false;
       launch<KMark>(c, nact);
       launch_counted<KFlip>(c, FM_C_NFLIP, nact);  // winners are queue entries: at most nact (and, being disjoint pairs, T / 2)

@@ -83,6 +83,56 @@ __global__ void __launch_bounds__(128) fm_kernel_deferred(DtCtx c) {
   }
 }
 
+// The north-star's warp-cooperative form of the flip check: FOUR lanes per queued
+// triangle.  Lanes 0..2 each fetch one vertex record of the triangle and run ONE edge's chain --
+// neighbour row word, opposite vertex record, in-circle filter -- so the three chains that a
+// thread per triangle walks one after the other run side by side; the triangle's vertices reach
+// the three evaluating lanes by shuffles, the verdict (first violated edge in edge order, or
+// "defer to the exact kernel") is taken from two ballots by lane 0.  Filter only, like
+// KCheckT<false>; selected with FM_CHECK_COOP4=1 for the A/B (results log).
+__global__ void __launch_bounds__(256, 4) fm_check_coop4(DtCtx c, int n) {
+  use_device_stamp(c);
+  const unsigned full = 0xffffffffu;
+  const int gt = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = gt >> 2, sub = gt & 3, lane = threadIdx.x & 31, base = lane & ~3;
+  const bool live = i < n, work = live && sub < 3;
+  int t = live ? c.active[i] : 0;
+  Row r = live ? c.row[t] : Row{I4{0, 0, 0, 0}, I4{0, 0, 0, 0}};
+  P4 mine = {0, 0, 0, 0}, opp = {0, 0, 0, 0};
+  if (work) {
+    mine = c.pts[geti(r.v, sub)];
+    const int ne = geti(r.a, sub);
+    const int d = ((const int*)c.row)[8 * (size_t)(ne >> 2) + (ne & 3)];
+    opp = c.pts[d];
+  }
+  P3 p[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    p[k].x = __shfl_sync(full, mine.x, base + k);
+    p[k].y = __shfl_sync(full, mine.y, base + k);
+    p[k].z = __shfl_sync(full, mine.z, base + k);
+  }
+  int s = -1;
+  if (work) s = incircle_fast(p[0], p[1], p[2], P3{opp.x, opp.y, opp.z});
+  const unsigned unsure = (__ballot_sync(full, work && s == 0) >> base) & 7u;
+  const unsigned viol = (__ballot_sync(full, work && s > 0) >> base) & 7u;
+  if (live && sub == 0) {
+    int fe = -1;
+    bool defer = false;
+    for (int k = 0; k < 3 && fe < 0 && !defer; k++) {   // the verdict a thread per triangle reaches edge by edge
+      if ((unsure >> k) & 1u) defer = true;
+      else if ((viol >> k) & 1u) fe = k;
+    }
+    if (defer) { defer_item(c, i); return; }
+    c.flip_edge[t] = fe;
+    if (fe >= 0) {
+      u64 key = vote_key(c.stamp, t);
+      atomicMin((unsigned long long*)&c.vote[t], (unsigned long long)key);
+      atomicMin((unsigned long long*)&c.vote[geti(r.a, fe) >> 2], (unsigned long long)key);
+    }
+  }
+}
+
 // All flip sub-rounds of one insertion round (or of one warm repair) in ONE cooperative
 // launch: check -> mark -> flip -> patch over the current queue, grid-wide barrier between
 // phases, until the queue is empty.  No host round trip per sub-round; the stamp lives in
