@@ -173,6 +173,15 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
     for (int i = gid; i < nact; i += gsz) KMark::run(c, i);
     grid.sync();
     const int nflip = vc[FM_C_NFLIP];  // the winners, compact (KMark)
+    if (nflip == 0) {
+      // Nobody flips: every queued triangle passed its tests (a triangle that lost a vote lost it
+      // to a winner), so nothing was queued for the next sub-round either -- the usual last,
+      // verifying sub-round.  Leave without the two barriers of the flip / patch phases.
+      if (gid == 0) c.counters[cur] = 0;
+      sub++;
+      stamp++;
+      break;
+    }
     for (int i = gid; i < nflip; i += gsz) KFlip::run(c, i);
     grid.sync();
     for (int i = gid; i < nflip; i += gsz) KPatch::run(c, i);
