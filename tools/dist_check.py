@@ -77,7 +77,12 @@ def main():
     it_c, md_c = c.lloyd(rho, max_iter=iters, tol=0.0, warm=True)
     # same trajectory, but not bit for bit: the connectivity was REPAIRED back to that of p (other slot
     # numbers than a fresh build, and a cell's quadrature sum starts at its lowest-numbered triangle)
-    block_set_ok = block_set_ok and np.abs(c.generators() - g_ref).max() < 1e-13
+    d_rerun = np.abs(c.generators() - g_ref).max(axis=1)
+    st_c = c.stats()
+    print(f"rank {rank}: after block upload generators == start set {block_set_ok}; rerun differs from the reference run by at most "
+          f"{d_rerun.max():.3e} ({int((d_rerun > 1e-13).sum())} cells above 1e-13; cold {st_c['cold']} warm {st_c['warm']}, "
+          f"iterations {it_c}, max_disp {md_c:.6e} vs {md_ref[-1]:.6e})", flush=True)
+    block_set_ok = block_set_ok and d_rerun.max() < 1e-12   # round-off of another summation order, grown over the iterations (measured 1.3e-13 at 655,362 x 12)
     all_ids = [None] * world
     dist.all_gather_object(all_ids, ids.tolist())
     cover_ok = sorted(v for part in all_ids for v in part) == list(range(1, n + 1))
