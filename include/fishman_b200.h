@@ -118,7 +118,11 @@ int fm_get_mpas_edges_on_edge(fm_handle* h, int32_t* n_edges_on_edge, int32_t* e
 /* Lloyd loop (no reference code).  Runs at most max_iter iterations of
  * triangulate -> circumcentres -> centroids -> generator update, stopping early when the
  * largest chord displacement is <= tol.  warm != 0 repairs the previous triangulation by
- * flip rounds when no triangle turned over, instead of rebuilding it. */
+ * flip rounds when no triangle turned over, instead of rebuilding it.  Warm iterations are queued
+ * in batches (FM_LLOYD_BATCH, default 32) and the host waits once per batch: the convergence
+ * test, the "a triangle turned over -> rebuild" decision and the statistics are taken on the
+ * device after every iteration, so the result is the same as with one host round trip per
+ * iteration -- same iteration count, same *max_disp, bit-identical generators. */
 int fm_lloyd(fm_handle* h, const fm_density* rho, int32_t max_iter, double tol, int32_t warm,
              int32_t* iters, double* max_disp);
 /* One iteration restricted to this rank's block of cells (fm_create_dist).  The caller
