@@ -139,11 +139,13 @@ struct DtCtx {
   const int* stamp_dev;        // when non-null the device-resident stamp (counters[FM_C_STAMP]) overrides
                                // `stamp` at kernel entry: the flip loop advances it on the device
   u64* vote;                   // per triangle: (~stamp << 32 | voter) claimed by atomicMin
-  int* flip_edge;              // per active triangle: edge it wants to flip, -1 none
+  int* flip_edge;              // per WINNING triangle of the sub-round: the edge it flips (KMark -> KFlip, KPatch)
   int* role;                   // per triangle: stamp << 2 | (1 winner, 2 partner)
   u64* mailbox;                // per (triangle, edge): stamp << 32 | new encoded neighbour
   int* amark;                  // per triangle: last stamp it was queued for
-  const int* active;           // triangles to check this sub-round
+  int* active;                 // triangles to check this sub-round; an entry is (slot | (edge + 1) << 29): the check
+                               // writes the edge it wants to flip INTO the entry (0: none), so that the mark phase
+                               // reads the queue alone for the many entries that want nothing (qe_* below)
   int n_active;
   int* next_active;            // queue for the next sub-round
   int* fliplist;               // the winners of the current sub-round's votes (KMark), compact:
@@ -273,10 +275,14 @@ FM_HD inline void defer_item(const DtCtx& c, int item) {
   c.slow[pos] = item;
 }
 
-FM_HD inline void queue_active(const DtCtx& c, int t, int stamp) {
+// queue entries: slot < 2^29 (fm_create refuses more), wanted edge + 1 in bits 29-30
+FM_HD inline int qe_tri(int e) { return e & 0x1fffffff; }
+FM_HD inline int qe_edge(int e) { return (e >> 29) - 1; }
+FM_HD inline int qe_make(int t, int fe) { return t | ((fe + 1) << 29); }
+FM_HD inline void queue_active(const DtCtx& c, int t, int stamp, int fe = -1) {
   if (FM_ATOMIC_EXCH32(&c.amark[t], stamp) != stamp) {
     int pos = FM_COUNT_INC(c.qcount);
-    c.next_active[pos] = t;
+    c.next_active[pos] = qe_make(t, fe);
   }
 }
 
@@ -438,9 +444,13 @@ struct KSplit {
         ((int*)&c.row[n].a)[e] = enc(childOf[k], 2);
       }
     }
-    c.row[t] = Row{I4{v.x, v.y, p, 0}, I4{enc(s1, 1), enc(s2, 0), outer[2], 0}};
-    c.row[s1] = Row{I4{v.y, v.z, p, 0}, I4{enc(s2, 1), enc(t, 0), outer[0], 0}};
-    c.row[s2] = Row{I4{v.z, v.x, p, 0}, I4{enc(t, 1), enc(s1, 0), outer[1], 0}};
+    // a.w: edges that are Delaunay BY CONSTRUCTION and need no test while the triangle stands (bit k =
+    // edge k).  The spokes of a fresh star are: a, b, c, p are in convex position on the sphere and p
+    // lies beyond the face (a,b,c), so (a,b,p), (b,c,p), (c,a,p) are the upper faces of a tetrahedron
+    // and meet convexly.  Only the edge inherited from the parent (edge 2) can be illegal.
+    c.row[t] = Row{I4{v.x, v.y, p, 0}, I4{enc(s1, 1), enc(s2, 0), outer[2], 3}};
+    c.row[s1] = Row{I4{v.y, v.z, p, 0}, I4{enc(s2, 1), enc(t, 0), outer[0], 3}};
+    c.row[s2] = Row{I4{v.z, v.x, p, 0}, I4{enc(t, 1), enc(s1, 0), outer[1], 3}};
     c.loc[p] = -1;
     c.v2t[p] = t;
     c.v2t[v.z] = s1;  // the only vertex that left slot t
@@ -468,31 +478,39 @@ FM_HD inline u64 vote_key(int stamp, int t) {
 template <bool EXACT>
 struct KCheckT {
   FM_HD static void run(const DtCtx& c, int i) {
-    int t = c.active[i];
+    int t = qe_tri(c.active[i]);
     Row r = c.row[t];
     I4 v = r.v, a = r.a;
 #if !defined(FM_CHECK_SEQUENTIAL)
-    // All gathers of the three tests are requested before the first is consumed (as the sweep does):
-    // the three opposite-vertex ids together, then the six vertex records together -- two dependent
-    // levels after the row instead of up to six when each edge's chain waited for the test before it.
+    // All gathers of the tests are requested before the first is consumed (as the sweep does): the
+    // opposite-vertex ids together, then the vertex records together -- two dependent levels after
+    // the row instead of up to six when each edge's chain waited for the test before it.
+    // In a build (c.cc == null: no generator moves while it runs) the edges a.w marks as Delaunay by
+    // construction are not tested at all: one test instead of three for a fresh child of a split,
+    // two for a triangle a flip made.  A warm repair tests every edge: the marks date from before
+    // the generators moved.
+    const int skip = c.cc ? 0 : (a.w & 7);
     const int* trow = (const int*)c.row;
-    int d0 = trow[8 * (size_t)(a.x >> 2) + (a.x & 3)];
-    int d1 = trow[8 * (size_t)(a.y >> 2) + (a.y & 3)];
-    int d2 = trow[8 * (size_t)(a.z >> 2) + (a.z & 3)];
+    int d0 = (skip & 1) ? -1 : trow[8 * (size_t)(a.x >> 2) + (a.x & 3)];
+    int d1 = (skip & 2) ? -1 : trow[8 * (size_t)(a.y >> 2) + (a.y & 3)];
+    int d2 = (skip & 4) ? -1 : trow[8 * (size_t)(a.z >> 2) + (a.z & 3)];
     P4 qa = c.pts[v.x], qb = c.pts[v.y], qc = c.pts[v.z];
-    P4 q0 = c.pts[d0], q1 = c.pts[d1], q2 = c.pts[d2];
+    const P4 zero = {0, 0, 0, 0};
+    P4 q0 = d0 >= 0 ? c.pts[d0] : zero, q1 = d1 >= 0 ? c.pts[d1] : zero, q2 = d2 >= 0 ? c.pts[d2] : zero;
     P3 pa{qa.x, qa.y, qa.z}, pb{qb.x, qb.y, qb.z}, pc{qc.x, qc.y, qc.z};
     int ia = (int)qa.id, ib = (int)qb.id, ic = (int)qc.id;
-    int fe = -1;
-    int s = incircle_t<EXACT>(pa, pb, pc, P3{q0.x, q0.y, q0.z}, ia, ib, ic, (int)q0.id);
-    if (!EXACT && s == 0) { defer_item(c, i); return; }
-    if (s > 0) fe = 0;
-    if (fe < 0) {
+    int fe = -1, s;
+    if (d0 >= 0) {
+      s = incircle_t<EXACT>(pa, pb, pc, P3{q0.x, q0.y, q0.z}, ia, ib, ic, (int)q0.id);
+      if (!EXACT && s == 0) { defer_item(c, i); return; }
+      if (s > 0) fe = 0;
+    }
+    if (fe < 0 && d1 >= 0) {
       s = incircle_t<EXACT>(pa, pb, pc, P3{q1.x, q1.y, q1.z}, ia, ib, ic, (int)q1.id);
       if (!EXACT && s == 0) { defer_item(c, i); return; }
       if (s > 0) fe = 1;
     }
-    if (fe < 0) {
+    if (fe < 0 && d2 >= 0) {
       s = incircle_t<EXACT>(pa, pb, pc, P3{q2.x, q2.y, q2.z}, ia, ib, ic, (int)q2.id);
       if (!EXACT && s == 0) { defer_item(c, i); return; }
       if (s > 0) fe = 2;
@@ -510,7 +528,7 @@ struct KCheckT {
       if (s > 0) { fe = k; break; }
     }
 #endif
-    c.flip_edge[t] = fe;
+    c.active[i] = qe_make(t, fe);   // a coalesced store instead of a scattered one to flip_edge[t]
     if (fe >= 0) {
       u64 key = vote_key(c.stamp, t);
       FM_ATOMIC_MIN64(&c.vote[t], key);
@@ -593,11 +611,10 @@ struct KSweepImpl {
     if (fe >= 0 && SHARDED) {
       c.req[FM_COUNT_INC(&c.counters[FM_C_REQ])] = (t << 2) | fe;
     } else if (fe >= 0) {
-      c.flip_edge[t] = fe;
       u64 key = vote_key(c.stamp, t);
       FM_ATOMIC_MIN64(&c.vote[t], key);
       FM_ATOMIC_MIN64(&c.vote[geti(a, fe) >> 2], key);
-      queue_active(c, t, c.stamp);
+      queue_active(c, t, c.stamp, fe);
     }
     if (c.cc) {
       bool dg;
@@ -622,22 +639,22 @@ typedef KSweepT<true> KSweep;
 struct KApply {
   FM_HD static void run(const DtCtx& c, int msg) {
     int t = msg >> 2, fe = msg & 3;
-    c.flip_edge[t] = fe;
     u64 key = vote_key(c.stamp, t);
     FM_ATOMIC_MIN64(&c.vote[t], key);
     FM_ATOMIC_MIN64(&c.vote[geti(c.row[t].a, fe) >> 2], key);
-    queue_active(c, t, c.stamp);
+    queue_active(c, t, c.stamp, fe);
   }
 };
 
 struct KMark {
   FM_HD static void run(const DtCtx& c, int i) {
-    int t = c.active[i];
-    int fe = c.flip_edge[t];
-    if (fe < 0) return;
+    const int e = c.active[i];
+    const int t = qe_tri(e), fe = qe_edge(e);
+    if (fe < 0) return;            // most entries: nothing but the (coalesced) queue was read
     int n = geti(c.row[t].a, fe) >> 2;
     u64 key = vote_key(c.stamp, t);
     if (c.vote[t] == key && c.vote[n] == key) {
+      c.flip_edge[t] = fe;         // for the flip and patch phases (winners only)
       c.role[t] = (c.stamp << 2) | 1;
       c.role[n] = (c.stamp << 2) | 2;
       // Only a fraction of the queue flips (measured: 6 of 32 lanes in a late insertion round);
@@ -695,8 +712,9 @@ struct KFlip {   // over fliplist[0 .. counters[FM_C_NFLIP])
         ((int*)&c.row[m].a)[em] = nw;
       }
     }
-    c.row[t] = Row{I4{va, vb, vd, e}, I4{outer[2], enc(n, 2), outer[0], 0}};  // v.w keeps e for KPatch
-    c.row[n] = Row{I4{va, vd, vc, 0}, I4{outer[3], outer[1], enc(t, 1), 0}};
+    // a.w: the new diagonal (a,d) is legal by the very test that ordered the flip (edge 1 of X, edge 2 of Y)
+    c.row[t] = Row{I4{va, vb, vd, e}, I4{outer[2], enc(n, 2), outer[0], 2}};  // v.w keeps e for KPatch
+    c.row[n] = Row{I4{va, vd, vc, 0}, I4{outer[3], outer[1], enc(t, 1), 4}};
     c.v2t[vb] = t;  // b left slot n, c left slot t (a and d only gained a triangle)
     c.v2t[vc] = n;
     if (c.ringc) {  // the rings of all four vertices changed

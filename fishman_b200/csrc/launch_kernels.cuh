@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(256, 4) fm_check_coop4(DtCtx c, int n) {
   const int gt = blockIdx.x * blockDim.x + threadIdx.x;
   const int i = gt >> 2, sub = gt & 3, lane = threadIdx.x & 31, base = lane & ~3;
   const bool live = i < n, work = live && sub < 3;
-  int t = live ? c.active[i] : 0;
+  int t = live ? qe_tri(c.active[i]) : 0;
   Row r = live ? c.row[t] : Row{I4{0, 0, 0, 0}, I4{0, 0, 0, 0}};
   P4 mine = {0, 0, 0, 0}, opp = {0, 0, 0, 0};
   if (work) {
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(256, 4) fm_check_coop4(DtCtx c, int n) {
       else if ((viol >> k) & 1u) fe = k;
     }
     if (defer) { defer_item(c, i); return; }
-    c.flip_edge[t] = fe;
+    c.active[i] = qe_make(t, fe);
     if (fe >= 0) {
       u64 key = vote_key(c.stamp, t);
       atomicMin((unsigned long long*)&c.vote[t], (unsigned long long)key);
