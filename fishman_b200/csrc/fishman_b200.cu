@@ -102,6 +102,11 @@ struct fm_handle {
     bool have = false;
   } mp;
   double* qbuf = nullptr;  // fm_quality: 16 histogram words, 6 extrema, 2 sums, then the block partials
+  // the density function staged as a table for the Lloyd kernel (Density::tab), for the parameters rho_tab_for
+  double* rho_tab = nullptr;
+  fm_density rho_tab_for = {};
+  bool rho_tab_ok = false;
+  double rho_tab_err = 0.0;
   // peer exchange: `pts` and a PeerSync block live in one arena that is exported over CUDA IPC
   // and mapped by the other ranks of the mesh (fm_peer_handle / fm_peer_attach)
   char* arena = nullptr;
@@ -585,7 +590,7 @@ extern "C" void fm_destroy(fm_handle* h) {
   {
     auto& m = h->mp;
     void* mptrs[] = {m.ring_edge, m.cells_on_vertex, m.edges_on_vertex, m.n_eoe, m.eoe, m.xyz_edge, m.lonlat_edge,
-                     m.edge5, m.area_cell, m.area_tri, m.kite_ring, m.kite_vtx, m.weights, m.sums, m.part, h->qbuf};
+                     m.edge5, m.area_cell, m.area_tri, m.kite_ring, m.kite_vtx, m.weights, m.sums, m.part, h->qbuf, h->rho_tab};
     for (void* p : mptrs)
       if (p) cudaFree(p);
   }
@@ -1041,6 +1046,8 @@ static void launch_peer_barrier(fm_handle* h, int phase) {
 }
 
 static Density make_density(const fm_density* rho);
+static Density make_density_h(fm_handle* h, const fm_density* rho);
+static int ensure_density_table(fm_handle* h, const fm_density* rho);
 static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded, bool dry = false);
 // Centroid stage of one iteration.  On a sharded mesh with attached peers the kernel runs
 // between two barriers: no rank overwrites generators another rank is still reading, and the
@@ -1052,7 +1059,7 @@ static void launch_centroid(fm_handle* h, const fm_density* rho, bool guarded, b
 }
 
 static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool guarded, bool dry) {
-  Density d = make_density(rho);
+  Density d = make_density_h(h, rho);
   VdCtx c = h->vd_ctx(&d);
   // guarded (warm iteration): skipped when the batch has halted -- converged, error, or a triangle
   // turned over (fm_flip_coop / fm_apply_requests' count turns that into the halt word)
@@ -1067,6 +1074,7 @@ static void launch_centroid_kernel(fm_handle* h, const fm_density* rho, bool gua
   size_t smem = sizeof(int) * kRingCap * B;
   h->prof_begin();
   if (d.kind == 0) fm_centroid_update<true><<<(cnt + B - 1) / B, B, smem, h->stream>>>(c, cnt);
+  else if (d.tab) fm_centroid_update<false, true><<<(cnt + B - 1) / B, B, smem, h->stream>>>(c, cnt);
   else fm_centroid_update<false><<<(cnt + B - 1) / B, B, smem, h->stream>>>(c, cnt);
   h->note_cuda(cudaGetLastError(), "centroid_update");
   h->prof_end("centroid_update", cnt);
@@ -1181,6 +1189,7 @@ static int lloyd_run(fm_handle* h, const fm_density* rho, int max_iter, double t
   }();
   int it = 0;
   double md = 0.0;
+  if (ensure_density_table(h, rho)) return 1;
   while (it < max_iter) {
     if (!(warm && h->have_dt)) {
       if (cold_iteration(h, rho, &md)) return 1;
@@ -1386,6 +1395,7 @@ extern "C" int fm_set_generators_block(fm_handle* h, const double* x, const doub
 extern "C" int fm_quality(fm_handle* h, const fm_density* rho, fm_quality_stats* out) {
   if (!h->have_dt) { h->fail("fm_quality before fm_triangulate"); return 1; }
   if (ensure_current(h, "fm_quality")) return 1;
+  if (ensure_density_table(h, rho)) return 1;
   if (!h->have_cc && circumcentres(h, false)) return 1;
   const int B = 128;
   int n = h->n, T = h->n_tri;
@@ -1430,12 +1440,100 @@ static Density make_density(const fm_density* rho) {
   else { d.cx = d.cy = 0; d.cz = 1; d.beta = 0; d.alpha = 1; d.gamma = 1; }
   d.k2 = 2.0 / d.alpha;
   d.c2 = -d.beta * d.k2;
+  d.tab = nullptr; d.tab_scale = 0.0; d.tab_n = 0;
+  return d;
+}
+
+// ---- the density function as a table (Density::tab).  rho of kind 1 depends on x only through the
+// arc distance d to the centre; written as a function of the chord u = 2 sin(d/2) in [0, 2] it is
+// analytic, and on kDensityIntervals equal intervals a degree-7 interpolant at Chebyshev nodes
+// reproduces it to round-off for any transition width a mesh can resolve.  The table is CHECKED
+// against the formula (25 samples per interval) and only used when its largest relative error is
+// below 2e-14; otherwise the kernel evaluates acos / exp directly as before.  FM_DENSITY_TABLE=0
+// switches it off.
+static const int kDensityIntervals = 512;
+// Largest relative error a table interval may have (25 samples against the formula).  The
+// interpolant has an ABSOLUTE error of a few 1e-17 (rho <= 1), i.e. a relative 1e-16 / rho where rho
+// is small (it bottoms out at gamma); a relative error eps of a weight moves a centroid by at most
+// eps times the cell diameter, so 2e-13 keeps the step far inside its 1e-12.  An interval that
+// misses it (the last one, next to the antipode of the centre, where the arc is not analytic in the
+// chord; transitions much narrower than an interval) is marked and evaluated by the formula.
+static const double kDensityTableTol = 2.0e-13;
+static double density_of_chord(const Density& d, double u) {
+  double arc = 2.0 * asin(u >= 2.0 ? 1.0 : 0.5 * u);
+  return 0.5 * (1.0 - d.gamma) * (tanh((d.beta - arc) / d.alpha) + 1.0) + d.gamma;
+}
+static double density_table(const Density& d, std::vector<double>& tab, int* bad_intervals) {
+  const int NI = kDensityIntervals, D = 8;
+  int n_bad = 0;
+  const double kPiH = 3.14159265358979323846;
+  tab.assign((size_t)NI * D, 0.0);
+  double T[8][8] = {{0}};   // T[k][m]: coefficient of s^m in the Chebyshev polynomial T_k
+  T[0][0] = 1.0; T[1][1] = 1.0;
+  for (int k = 2; k < D; k++)
+    for (int m = 0; m < D; m++) T[k][m] = (m > 0 ? 2.0 * T[k - 1][m - 1] : 0.0) - T[k - 2][m];
+  double worst = 0.0;
+  for (int i = 0; i < NI; i++) {
+    const double a = 2.0 * i / NI, half = 1.0 / NI, mid = a + half;
+    double f[8], c[8];
+    for (int j = 0; j < D; j++) f[j] = density_of_chord(d, mid + half * cos(kPiH * (j + 0.5) / D));
+    for (int k = 0; k < D; k++) {
+      double acc = 0.0;
+      for (int j = 0; j < D; j++) acc += f[j] * cos(kPiH * k * (j + 0.5) / D);
+      c[k] = acc * (k == 0 ? 1.0 : 2.0) / D;
+    }
+    double* out = tab.data() + (size_t)i * D;
+    for (int m = 0; m < D; m++) {
+      double acc = 0.0;
+      for (int k = 0; k < D; k++) acc += c[k] * T[k][m];
+      out[m] = acc;
+    }
+    double err_i = 0.0;
+    for (int q = 0; q <= 24; q++) {
+      const double sx = -1.0 + q / 12.0;
+      double p = out[D - 1];
+      for (int m = D - 2; m >= 0; m--) p = p * sx + out[m];
+      const double want = density_of_chord(d, mid + half * sx);
+      const double err = fabs(p / want - 1.0);
+      if (!(err <= err_i)) err_i = err;   // (NaN counts as failure)
+    }
+    if (!(err_i <= kDensityTableTol)) { out[D - 1] = nan(""); n_bad++; }   // this interval is evaluated directly
+    else if (err_i > worst) worst = err_i;
+  }
+  if (bad_intervals) *bad_intervals = n_bad;
+  return worst;
+}
+static bool density_table_wanted() {
+  const char* e = getenv("FM_DENSITY_TABLE");
+  return !(e && atoi(e) == 0);
+}
+// Makes sure the handle's table belongs to rho (builds and uploads it when the parameters changed)
+static int ensure_density_table(fm_handle* h, const fm_density* rho) {
+  if (!rho || rho->kind != 1) return 0;
+  if (h->rho_tab && same_density(rho, h->rho_tab_for)) return 0;
+  Density d = make_density(rho);
+  std::vector<double> tab;
+  int bad = 0;
+  h->rho_tab_err = density_table(d, tab, &bad);
+  h->rho_tab_ok = density_table_wanted() && bad <= kDensityIntervals / 4;   // mostly unfittable: not worth the detour
+  if (!h->rho_tab) FM_CUDA(dalloc(&h->rho_tab, (size_t)kDensityIntervals * 8));
+  FM_CUDA(cudaMemcpyAsync(h->rho_tab, tab.data(), sizeof(double) * tab.size(), cudaMemcpyHostToDevice, h->stream));
+  FM_CUDA(cudaStreamSynchronize(h->stream));
+  h->rho_tab_for = *rho;
+  if (h->warm_graph) { cudaGraphExecDestroy(h->warm_graph); h->warm_graph = nullptr; }
+  return 0;
+}
+static Density make_density_h(fm_handle* h, const fm_density* rho) {
+  Density d = make_density(rho);
+  if (d.kind == 1 && h->rho_tab && h->rho_tab_ok && same_density(rho, h->rho_tab_for)) {
+    d.tab = h->rho_tab; d.tab_n = kDensityIntervals; d.tab_scale = 0.5 * kDensityIntervals;
+  }
   return d;
 }
 
 __global__ void fm_density_points(Density d, long long n, const double* x, const double* y, const double* z, double* out) {
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (i < n) out[i] = density_node(d, x[i], y[i], z[i], 1.0);
+  if (i < n) out[i] = d.tab ? density_node<true>(d, x[i], y[i], z[i], 1.0) : density_node<false>(d, x[i], y[i], z[i], 1.0);
 }
 extern "C" int fm_density_eval(const fm_density* rho, int64_t n, const double* x, const double* y, const double* z,
                                double* out) {
@@ -1449,10 +1547,23 @@ extern "C" int fm_density_eval(const fm_density* rho, int64_t n, const double* x
   bool ok = cudaMemcpy(dev, x, bytes, cudaMemcpyHostToDevice) == cudaSuccess &&
             cudaMemcpy(dev + n, y, bytes, cudaMemcpyHostToDevice) == cudaSuccess &&
             cudaMemcpy(dev + 2 * n, z, bytes, cudaMemcpyHostToDevice) == cudaSuccess;
+  double* dtab = nullptr;
   if (ok) {
-    fm_density_points<<<(unsigned)((n + 255) / 256), 256>>>(make_density(rho), n, dev, dev + n, dev + 2 * n, dev + 3 * n);
+    Density d = make_density(rho);
+    const char* force = getenv("FM_DENSITY_TABLE");
+    if (d.kind == 1 && force && atoi(force) == 1) {   // FM_DENSITY_TABLE=1: through the table the Lloyd kernel uses (default: the formula)
+      std::vector<double> tab;
+      int bad = 0;
+      density_table(d, tab, &bad);
+      if (bad <= kDensityIntervals / 4 && cudaMalloc((void**)&dtab, sizeof(double) * tab.size()) == cudaSuccess &&
+          cudaMemcpy(dtab, tab.data(), sizeof(double) * tab.size(), cudaMemcpyHostToDevice) == cudaSuccess) {
+        d.tab = dtab; d.tab_n = kDensityIntervals; d.tab_scale = 0.5 * kDensityIntervals;
+      }
+    }
+    fm_density_points<<<(unsigned)((n + 255) / 256), 256>>>(d, n, dev, dev + n, dev + 2 * n, dev + 3 * n);
     ok = cudaMemcpy(out, dev + 3 * n, bytes, cudaMemcpyDeviceToHost) == cudaSuccess;
   }
+  if (dtab) cudaFree(dtab);
   cudaFree(dev);
   if (!ok) snprintf(g_create_err, sizeof g_create_err, "fm_density_eval: %s", cudaGetErrorString(cudaGetLastError()));
   return ok ? 0 : 1;

@@ -251,9 +251,13 @@ __global__ void fm_subround_end(int* counters, int cur, int nact) {
 #ifndef FM_CENTROID_WARPS_RHO
 #define FM_CENTROID_WARPS_RHO 16   // 128 registers
 #endif
-template <bool UNIFORM>
+#ifndef FM_CENTROID_WARPS_TAB
+#define FM_CENTROID_WARPS_TAB 24   // density from the table: resident warps per SM the register budget is set for
+#endif
+template <bool UNIFORM, bool TABLE = false>
 __global__ void __launch_bounds__(UNIFORM ? FM_CENTROID_BLOCK : FM_CENTROID_BLOCK_RHO,
-                                  UNIFORM ? FM_CENTROID_WARPS * 32 / FM_CENTROID_BLOCK : FM_CENTROID_WARPS_RHO * 32 / FM_CENTROID_BLOCK_RHO)
+                                  UNIFORM ? FM_CENTROID_WARPS * 32 / FM_CENTROID_BLOCK
+                                          : (TABLE ? FM_CENTROID_WARPS_TAB : FM_CENTROID_WARPS_RHO) * 32 / FM_CENTROID_BLOCK_RHO)
     fm_centroid_update(const VdCtx c, int n) {
   extern __shared__ int ring_smem[];
   int j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -265,7 +269,7 @@ __global__ void __launch_bounds__(UNIFORM ? FM_CENTROID_BLOCK : FM_CENTROID_BLOC
   }
   if (c.abort_flag && *c.abort_flag) return;  // = the halt word (launch_centroid_kernel)
   double disp = 0.0;
-  if (j < n) disp = KCentroid::compute<UNIFORM>(c, c.cell_begin + j, ring_smem + threadIdx.x, blockDim.x);
+  if (j < n) disp = KCentroid::compute<UNIFORM, TABLE>(c, c.cell_begin + j, ring_smem + threadIdx.x, blockDim.x);
   for (int o = 16; o > 0; o >>= 1) disp = fmax(disp, __shfl_xor_sync(0xffffffffu, disp, o));
   // one atomicMax per WARP at most: only a warp that beats the maximum seen so far sends one
   // (the word is read first; after the first few warps almost nobody does)

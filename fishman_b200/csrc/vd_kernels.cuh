@@ -34,6 +34,13 @@ struct Density {   // the first seven members: same layout as fm_density in incl
   int kind;        // 0 uniform, 1 tanh refinement
   double cx, cy, cz, beta, alpha, gamma;
   double k2, c2;   // 2/alpha and -2 beta/alpha, set by the launcher: -2 (beta - d)/alpha = d k2 + c2
+  // The density function staged as a table (north-star (c)): rho as a function of the CHORD
+  // u = |x - c| in [0, 2] (analytic there, unlike rho(dot) at dot = 1), tab_n intervals with a
+  // degree-7 polynomial in s = 2 frac - 1 each (8 doubles per interval, 64-byte aligned), built and
+  // checked on the host by the launcher (fishman_b200.cu: density_table); null = evaluate directly.
+  const double* tab;
+  double tab_scale;   // tab_n / 2: intervals per unit of chord
+  int tab_n;
 };
 
 struct VdCtx {
@@ -205,7 +212,7 @@ __device__ __forceinline__ double fm_exp(double t) {  // t in [-700, 700]
 }
 #endif
 // density at the projected node q/|q|, given q and inv = 1/|q|
-FM_HD inline double density_node(const Density& r, double qx, double qy, double qz, double inv) {
+FM_HD inline double density_node_direct(const Density& r, double qx, double qy, double qz, double inv) {
 #if defined(__CUDA_ARCH__)
   const double dot = fma(qz, r.cz, fma(qy, r.cy, qx * r.cx)) * inv;
   const double d = fm_acos(dot);
@@ -216,6 +223,43 @@ FM_HD inline double density_node(const Density& r, double qx, double qy, double 
 #else
   return density_eval(r, qx * inv, qy * inv, qz * inv);
 #endif
+}
+#if defined(__CUDACC__)
+// the rare interval the table could not fit (marked by a NaN): out of line, so that the table kernel
+// does not carry the registers of acos / exp through its quadrature
+__device__ __noinline__ double density_node_slow(const Density& r, double dot) {
+  const double d = fm_acos(dot);
+  double t = fma(d, r.k2, r.c2);
+  t = t > 700.0 ? 700.0 : t;
+  t = t < -700.0 ? -700.0 : t;
+  return fma(1.0 - r.gamma, fm_rcp(1.0 + fm_exp(t)), r.gamma);
+}
+#endif
+template <bool TABLE>
+FM_HD inline double density_node(const Density& r, double qx, double qy, double qz, double inv) {
+#if defined(__CUDA_ARCH__)
+  if (TABLE) {
+    // ~20 fp64 instructions instead of ~89 (acos + exp + reciprocal): chord, interval, Horner
+    const double dot = fma(qz, r.cz, fma(qy, r.cy, qx * r.cx)) * inv;
+    double w = fma(-2.0, dot, 2.0);                 // |x - c|^2 = 2 - 2 x.c
+    w = w > 0.0 ? w : 0.0;
+    const double u = w > 0.0 ? w * fm_rsqrt(w) : 0.0;
+    const double f = u * r.tab_scale;
+    int k = (int)f;
+    k = k < r.tab_n ? k : r.tab_n - 1;
+    const double sx = fma(2.0, f - (double)k, -1.0);
+    struct alignas(32) D4 { double x, y, z, w; };   // two 256-bit loads per evaluation
+    const D4* c4 = reinterpret_cast<const D4*>(r.tab) + 2 * (size_t)k;
+    const D4 lo = c4[0], hi = c4[1];
+    if (hi.w != hi.w) return density_node_slow(r, dot);
+    double p = hi.w;   // Horner (Estrin's three-level tree measured the same: 0.585 against 0.578 ms)
+    p = fma(p, sx, hi.z); p = fma(p, sx, hi.y); p = fma(p, sx, hi.x);
+    p = fma(p, sx, lo.w); p = fma(p, sx, lo.z); p = fma(p, sx, lo.y); p = fma(p, sx, lo.x);
+    p = p < r.gamma ? r.gamma : p;   // the interpolant may leave [gamma, 1] by a rounding
+    return p > 1.0 ? 1.0 : p;
+  }
+#endif
+  return density_node_direct(r, qx, qy, qz, inv);
 }
 
 // degree-5 seven-point rule on a triangle (barycentric weights of g, c_j, c_j+1)
@@ -251,7 +295,7 @@ FM_HD inline double fm_rsqrt_q(double v) {
 //   |q|^2 = S.S + 2 kappa S.v + kappa^2 v.v,      sum_k w_k q_k/|q_k| = cS S + cg g + ca a + cb b
 // with scalar coefficients: the node vectors themselves are only formed when the density has
 // to be evaluated at them.  gg, aa, bb are the squared norms of g, a, b.
-template <bool UNIFORM>
+template <bool UNIFORM, bool TABLE>
 FM_HD inline void quad_subtriangle(const Density& r, const P3& g, const P3& a, const P3& b, double gg,
                                    double aa, double bb, double& M0, double& M1, double& M2) {
   const double k1 = (FM_QB1 - FM_QA1) / FM_QA1, k2 = (FM_QB2 - FM_QA2) / FM_QA2;
@@ -276,13 +320,13 @@ FM_HD inline void quad_subtriangle(const Density& r, const P3& g, const P3& a, c
   double w1g = FM_QW1 * i1g, w1a = FM_QW1 * i1a, w1b = FM_QW1 * i1b;
   double w2g = FM_QW2 * i2g, w2a = FM_QW2 * i2a, w2b = FM_QW2 * i2b;
   if (!UNIFORM) {  // density at the projected nodes q^ = (S + kappa v) / |q|
-    w0 *= density_node(r, S0, S1, S2, i0);
-    w1g *= density_node(r, fma(k1, g.x, S0), fma(k1, g.y, S1), fma(k1, g.z, S2), i1g);
-    w1a *= density_node(r, fma(k1, a.x, S0), fma(k1, a.y, S1), fma(k1, a.z, S2), i1a);
-    w1b *= density_node(r, fma(k1, b.x, S0), fma(k1, b.y, S1), fma(k1, b.z, S2), i1b);
-    w2g *= density_node(r, fma(k2, g.x, S0), fma(k2, g.y, S1), fma(k2, g.z, S2), i2g);
-    w2a *= density_node(r, fma(k2, a.x, S0), fma(k2, a.y, S1), fma(k2, a.z, S2), i2a);
-    w2b *= density_node(r, fma(k2, b.x, S0), fma(k2, b.y, S1), fma(k2, b.z, S2), i2b);
+    w0 *= density_node<TABLE>(r, S0, S1, S2, i0);
+    w1g *= density_node<TABLE>(r, fma(k1, g.x, S0), fma(k1, g.y, S1), fma(k1, g.z, S2), i1g);
+    w1a *= density_node<TABLE>(r, fma(k1, a.x, S0), fma(k1, a.y, S1), fma(k1, a.z, S2), i1a);
+    w1b *= density_node<TABLE>(r, fma(k1, b.x, S0), fma(k1, b.y, S1), fma(k1, b.z, S2), i1b);
+    w2g *= density_node<TABLE>(r, fma(k2, g.x, S0), fma(k2, g.y, S1), fma(k2, g.z, S2), i2g);
+    w2a *= density_node<TABLE>(r, fma(k2, a.x, S0), fma(k2, a.y, S1), fma(k2, a.z, S2), i2a);
+    w2b *= density_node<TABLE>(r, fma(k2, b.x, S0), fma(k2, b.y, S1), fma(k2, b.z, S2), i2b);
   }
   double cS = w0 + ((w1g + w1a) + w1b) + ((w2g + w2a) + w2b);
   double cg = fma(k1, w1g, k2 * w2g), ca = fma(k1, w1a, k2 * w2a), cb = fma(k1, w1b, k2 * w2b);
@@ -349,7 +393,7 @@ struct KCentroid {
   // scratch for kRingCap triangle ids (shared memory on the device).  The accumulation starts
   // at the LOWEST triangle id of the ring, whatever triangle v2t points at, so the result does
   // not depend on which incident triangle happens to be remembered.
-  template <bool UNIFORM>
+  template <bool UNIFORM, bool TABLE = false>
   FM_HD static double compute(const VdCtx& c, int i, int* ring, int stride) {
     P4 gq = c.pts[i];
     P3 g{gq.x, gq.y, gq.z};
@@ -423,7 +467,7 @@ struct KCentroid {
         j = (j + 1 == d) ? 0 : j + 1;
         P4 qn = c.cc[ring[j * stride]];  // prefetch: consumed in the next iteration
         double bb = qb.x * qb.x + qb.y * qb.y + qb.z * qb.z;
-        quad_subtriangle<UNIFORM>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gg, aa, bb, M0, M1, M2);
+        quad_subtriangle<UNIFORM, TABLE>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gg, aa, bb, M0, M1, M2);
         qa = qb;
         qb = qn;
         aa = bb;
@@ -436,7 +480,7 @@ struct KCentroid {
         t = ring_next(c, t, k);
         P4 qb = c.cc[t];
         double bb = qb.x * qb.x + qb.y * qb.y + qb.z * qb.z;
-        quad_subtriangle<UNIFORM>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gg, aa, bb, M0, M1, M2);
+        quad_subtriangle<UNIFORM, TABLE>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gg, aa, bb, M0, M1, M2);
         qa = qb;
         aa = bb;
       }

@@ -44,9 +44,13 @@ typedef struct fm_density {
   double cx, cy, cz, beta, alpha, gamma;
 } fm_density;
 
-/* rho at n unit vectors, evaluated on the device by the code the Lloyd kernel uses (host
- * pointers in and out; no mesh needed).  For diagnostics and for the parity tests of the
- * density function itself. */
+/* rho at n unit vectors, evaluated on the device (host pointers in and out; no mesh needed), for
+ * diagnostics and for the parity tests of the density function itself.  By default through the
+ * formula (device acos / exp without library calls, relative error ~1e-16); with the environment
+ * variable FM_DENSITY_TABLE=1 through the staged table the Lloyd kernel reads (rho as a piecewise
+ * degree-7 polynomial of the chord to the centre, checked on the host to 2e-13 per interval;
+ * intervals that miss it are evaluated by the formula).  FM_DENSITY_TABLE=0 makes the Lloyd kernel
+ * use the formula as well. */
 int fm_density_eval(const fm_density* rho, int64_t n, const double* x, const double* y, const double* z,
                     double* out);
 
