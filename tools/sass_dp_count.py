@@ -20,7 +20,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "fishman_b200", "libfishman_b200.so")
-FUNC = "_ZN2fm18fm_centroid_updateILb1EEEvNS_5VdCtxEi"
+FUNC = "_ZN2fm18fm_centroid_updateILb1ELb0EEEvNS_5VdCtxEi"
 
 
 def csrc_sha16():
