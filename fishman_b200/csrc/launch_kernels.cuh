@@ -252,7 +252,7 @@ __global__ void fm_subround_end(int* counters, int cur, int nact) {
 #define FM_CENTROID_WARPS_RHO 16   // 128 registers
 #endif
 #ifndef FM_CENTROID_WARPS_TAB
-#define FM_CENTROID_WARPS_TAB 24   // density from the table: resident warps per SM the register budget is set for
+#define FM_CENTROID_WARPS_TAB 18   // density from the table: resident warps per SM the register budget is set for (96 registers, no spill; A/B 16..24 in profiles/r02_ab_centroid_density.txt)
 #endif
 template <bool UNIFORM, bool TABLE = false>
 __global__ void __launch_bounds__(UNIFORM ? FM_CENTROID_BLOCK : FM_CENTROID_BLOCK_RHO,

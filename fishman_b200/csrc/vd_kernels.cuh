@@ -212,18 +212,6 @@ __device__ __forceinline__ double fm_exp(double t) {  // t in [-700, 700]
 }
 #endif
 // density at the projected node q/|q|, given q and inv = 1/|q|
-FM_HD inline double density_node_direct(const Density& r, double qx, double qy, double qz, double inv) {
-#if defined(__CUDA_ARCH__)
-  const double dot = fma(qz, r.cz, fma(qy, r.cy, qx * r.cx)) * inv;
-  const double d = fm_acos(dot);
-  double t = fma(d, r.k2, r.c2);   // -2 (beta - d)/alpha
-  t = t > 700.0 ? 700.0 : t;
-  t = t < -700.0 ? -700.0 : t;
-  return fma(1.0 - r.gamma, fm_rcp(1.0 + fm_exp(t)), r.gamma);
-#else
-  return density_eval(r, qx * inv, qy * inv, qz * inv);
-#endif
-}
 #if defined(__CUDACC__)
 // the rare interval the table could not fit (marked by a NaN): out of line, so that the table kernel
 // does not carry the registers of acos / exp through its quadrature
@@ -235,12 +223,12 @@ __device__ __noinline__ double density_node_slow(const Density& r, double dot) {
   return fma(1.0 - r.gamma, fm_rcp(1.0 + fm_exp(t)), r.gamma);
 }
 #endif
+// density at the unit vector whose product with the centre is `dot`
 template <bool TABLE>
-FM_HD inline double density_node(const Density& r, double qx, double qy, double qz, double inv) {
+FM_HD inline double density_dot(const Density& r, double dot) {
 #if defined(__CUDA_ARCH__)
   if (TABLE) {
     // ~20 fp64 instructions instead of ~89 (acos + exp + reciprocal): chord, interval, Horner
-    const double dot = fma(qz, r.cz, fma(qy, r.cy, qx * r.cx)) * inv;
     double w = fma(-2.0, dot, 2.0);                 // |x - c|^2 = 2 - 2 x.c
     w = w > 0.0 ? w : 0.0;
     const double u = w > 0.0 ? w * fm_rsqrt(w) : 0.0;
@@ -258,8 +246,24 @@ FM_HD inline double density_node(const Density& r, double qx, double qy, double 
     p = p < r.gamma ? r.gamma : p;   // the interpolant may leave [gamma, 1] by a rounding
     return p > 1.0 ? 1.0 : p;
   }
+  const double d = fm_acos(dot);
+  double t = fma(d, r.k2, r.c2);   // -2 (beta - d)/alpha
+  t = t > 700.0 ? 700.0 : t;
+  t = t < -700.0 ? -700.0 : t;
+  return fma(1.0 - r.gamma, fm_rcp(1.0 + fm_exp(t)), r.gamma);
+#else
+  double dd = acos(fmax(fmin(dot, 1.0), -1.0));
+  return 0.5 * (1.0 - r.gamma) * (tanh((r.beta - dd) / r.alpha) + 1.0) + r.gamma;
 #endif
-  return density_node_direct(r, qx, qy, qz, inv);
+}
+// density at the projected node q/|q|, given q and inv = 1/|q|
+template <bool TABLE>
+FM_HD inline double density_node(const Density& r, double qx, double qy, double qz, double inv) {
+#if defined(__CUDA_ARCH__)
+  return density_dot<TABLE>(r, fma(qz, r.cz, fma(qy, r.cy, qx * r.cx)) * inv);
+#else
+  return density_eval(r, qx * inv, qy * inv, qz * inv);
+#endif
 }
 
 // degree-5 seven-point rule on a triangle (barycentric weights of g, c_j, c_j+1)
@@ -294,46 +298,54 @@ FM_HD inline double fm_rsqrt_q(double v) {
 // Only q/|q| enters, so each node is taken as q = S + kappa v (kappa = (B - A)/A) and
 //   |q|^2 = S.S + 2 kappa S.v + kappa^2 v.v,      sum_k w_k q_k/|q_k| = cS S + cg g + ca a + cb b
 // with scalar coefficients: the node vectors themselves are only formed when the density has
-// to be evaluated at them.  gg, aa, bb are the squared norms of g, a, b.
+// to be evaluated at them.
+// General form (a density, or a ring too long for the staged one).  g, a and b are unit vectors to
+// a few 1e-16, so g.g = a.a = b.b = 1 inside |q|^2 (see quad_uniform); and the product of a node
+// with the density's centre c is  q.c = S.c + kappa v.c  with S.c = g.c + a.c + b.c: the node
+// vectors are never formed, three products with c per ring vertex replace one per node.  gc, ac,
+// bc: products of g, a, b with the centre (unused when UNIFORM).
 template <bool UNIFORM, bool TABLE>
-FM_HD inline void quad_subtriangle(const Density& r, const P3& g, const P3& a, const P3& b, double gg,
-                                   double aa, double bb, double& M0, double& M1, double& M2) {
+FM_HD inline void quad_subtriangle(const Density& r, const P3& g, const P3& a, const P3& b, double gc,
+                                   double ac, double bc, double& M0, double& M1, double& M2) {
   const double k1 = (FM_QB1 - FM_QA1) / FM_QA1, k2 = (FM_QB2 - FM_QA2) / FM_QA2;
   double u0 = a.x - g.x, u1 = a.y - g.y, u2 = a.z - g.z;
   double v0 = b.x - g.x, v1 = b.y - g.y, v2 = b.z - g.z;
   double c0 = u1 * v2 - u2 * v1, c1 = u2 * v0 - u0 * v2, c2 = u0 * v1 - u1 * v0;
   double n2 = c0 * c0 + c1 * c1 + c2 * c2;
   double A = n2 > 0.0 ? 0.5 * n2 * fm_rsqrt(n2) : 0.0;  // planar area; coincident circumcentres give 0
-  double S0 = g.x + a.x + b.x, S1 = g.y + a.y + b.y, S2 = g.z + a.z + b.z;
-  double SS = S0 * S0 + S1 * S1 + S2 * S2;
-  double Sg = S0 * g.x + S1 * g.y + S2 * g.z;
-  double Sa = S0 * a.x + S1 * a.y + S2 * a.z;
-  double Sb = S0 * b.x + S1 * b.y + S2 * b.z;
+  double ga = g.x * a.x + g.y * a.y + g.z * a.z;
+  double gb = g.x * b.x + g.y * b.y + g.z * b.z;
+  double ab = a.x * b.x + a.y * b.y + a.z * b.z;
+  double Sg = 1.0 + ga + gb, Sa = ga + 1.0 + ab, Sb = gb + ab + 1.0;
+  double SS = Sg + Sa + Sb;
+  const double S1 = SS + k1 * k1, S2 = SS + k2 * k2;   // |S + kappa v|^2 = S.S + kappa^2 + 2 kappa S.v
   double i0 = fm_rsqrt(SS);
-  double i1g = fm_rsqrt(fma(k1 * k1, gg, fma(2.0 * k1, Sg, SS)));
-  double i1a = fm_rsqrt(fma(k1 * k1, aa, fma(2.0 * k1, Sa, SS)));
-  double i1b = fm_rsqrt(fma(k1 * k1, bb, fma(2.0 * k1, Sb, SS)));
-  double i2g = fm_rsqrt(fma(k2 * k2, gg, fma(2.0 * k2, Sg, SS)));
-  double i2a = fm_rsqrt(fma(k2 * k2, aa, fma(2.0 * k2, Sa, SS)));
-  double i2b = fm_rsqrt(fma(k2 * k2, bb, fma(2.0 * k2, Sb, SS)));
+  double i1g = fm_rsqrt(fma(2.0 * k1, Sg, S1));
+  double i1a = fm_rsqrt(fma(2.0 * k1, Sa, S1));
+  double i1b = fm_rsqrt(fma(2.0 * k1, Sb, S1));
+  double i2g = fm_rsqrt(fma(2.0 * k2, Sg, S2));
+  double i2a = fm_rsqrt(fma(2.0 * k2, Sa, S2));
+  double i2b = fm_rsqrt(fma(2.0 * k2, Sb, S2));
   double w0 = FM_QW0 * i0;
   double w1g = FM_QW1 * i1g, w1a = FM_QW1 * i1a, w1b = FM_QW1 * i1b;
   double w2g = FM_QW2 * i2g, w2a = FM_QW2 * i2a, w2b = FM_QW2 * i2b;
   if (!UNIFORM) {  // density at the projected nodes q^ = (S + kappa v) / |q|
-    w0 *= density_node<TABLE>(r, S0, S1, S2, i0);
-    w1g *= density_node<TABLE>(r, fma(k1, g.x, S0), fma(k1, g.y, S1), fma(k1, g.z, S2), i1g);
-    w1a *= density_node<TABLE>(r, fma(k1, a.x, S0), fma(k1, a.y, S1), fma(k1, a.z, S2), i1a);
-    w1b *= density_node<TABLE>(r, fma(k1, b.x, S0), fma(k1, b.y, S1), fma(k1, b.z, S2), i1b);
-    w2g *= density_node<TABLE>(r, fma(k2, g.x, S0), fma(k2, g.y, S1), fma(k2, g.z, S2), i2g);
-    w2a *= density_node<TABLE>(r, fma(k2, a.x, S0), fma(k2, a.y, S1), fma(k2, a.z, S2), i2a);
-    w2b *= density_node<TABLE>(r, fma(k2, b.x, S0), fma(k2, b.y, S1), fma(k2, b.z, S2), i2b);
+    const double Sc = (gc + ac) + bc;
+    w0 *= density_dot<TABLE>(r, Sc * i0);
+    w1g *= density_dot<TABLE>(r, fma(k1, gc, Sc) * i1g);
+    w1a *= density_dot<TABLE>(r, fma(k1, ac, Sc) * i1a);
+    w1b *= density_dot<TABLE>(r, fma(k1, bc, Sc) * i1b);
+    w2g *= density_dot<TABLE>(r, fma(k2, gc, Sc) * i2g);
+    w2a *= density_dot<TABLE>(r, fma(k2, ac, Sc) * i2a);
+    w2b *= density_dot<TABLE>(r, fma(k2, bc, Sc) * i2b);
   }
   double cS = w0 + ((w1g + w1a) + w1b) + ((w2g + w2a) + w2b);
-  double cg = fma(k1, w1g, k2 * w2g), ca = fma(k1, w1a, k2 * w2a), cb = fma(k1, w1b, k2 * w2b);
-  double s0 = fma(cb, b.x, fma(ca, a.x, fma(cg, g.x, cS * S0)));
-  double s1 = fma(cb, b.y, fma(ca, a.y, fma(cg, g.y, cS * S1)));
-  double s2 = fma(cb, b.z, fma(ca, a.z, fma(cg, g.z, cS * S2)));
-  M0 = fma(A, s0, M0); M1 = fma(A, s1, M1); M2 = fma(A, s2, M2);
+  double tg = A * (cS + fma(k1, w1g, k2 * w2g));
+  double ta = A * (cS + fma(k1, w1a, k2 * w2a));
+  double tb = A * (cS + fma(k1, w1b, k2 * w2b));
+  M0 = fma(tb, b.x, fma(ta, a.x, fma(tg, g.x, M0)));
+  M1 = fma(tb, b.y, fma(ta, a.y, fma(tg, g.y, M1)));
+  M2 = fma(tb, b.z, fma(ta, a.z, fma(tg, g.z, M2)));
 }
 
 // Uniform density: the same rule regrouped around the ring.  Per ring vertex c the product
@@ -441,7 +453,6 @@ struct KCentroid {
     // extra address arithmetic and cache pressure cost more than the latency hidden;
     // profiles/r02_i_ab_centroid_prefetch.txt.)
     double M0 = 0.0, M1 = 0.0, M2 = 0.0;
-    const double gg = g.x * g.x + g.y * g.y + g.z * g.z;
     if (UNIFORM && d <= kRingCap) {
       int j = jmin;
       double Mg = 0.0;
@@ -462,27 +473,29 @@ struct KCentroid {
       P4 qa = c.cc[tmin];
       j = (j + 1 == d) ? 0 : j + 1;
       P4 qb = c.cc[ring[j * stride]];
-      double aa = qa.x * qa.x + qa.y * qa.y + qa.z * qa.z;
+      const double gc = g.x * c.rho.cx + g.y * c.rho.cy + g.z * c.rho.cz;
+      double ac = qa.x * c.rho.cx + qa.y * c.rho.cy + qa.z * c.rho.cz;
       for (int s = 0; s < d; s++) {
         j = (j + 1 == d) ? 0 : j + 1;
         P4 qn = c.cc[ring[j * stride]];  // prefetch: consumed in the next iteration
-        double bb = qb.x * qb.x + qb.y * qb.y + qb.z * qb.z;
-        quad_subtriangle<UNIFORM, TABLE>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gg, aa, bb, M0, M1, M2);
+        double bc = qb.x * c.rho.cx + qb.y * c.rho.cy + qb.z * c.rho.cz;
+        quad_subtriangle<UNIFORM, TABLE>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gc, ac, bc, M0, M1, M2);
         qa = qb;
         qb = qn;
-        aa = bb;
+        ac = bc;
       }
     } else {  // long ring: walk again from the lowest triangle
       t = tmin; k = kmin;
       P4 qa = c.cc[t];
-      double aa = qa.x * qa.x + qa.y * qa.y + qa.z * qa.z;
+      const double gc = g.x * c.rho.cx + g.y * c.rho.cy + g.z * c.rho.cz;
+      double ac = qa.x * c.rho.cx + qa.y * c.rho.cy + qa.z * c.rho.cz;
       for (int s = 0; s < d; s++) {
         t = ring_next(c, t, k);
         P4 qb = c.cc[t];
-        double bb = qb.x * qb.x + qb.y * qb.y + qb.z * qb.z;
-        quad_subtriangle<UNIFORM, TABLE>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gg, aa, bb, M0, M1, M2);
+        double bc = qb.x * c.rho.cx + qb.y * c.rho.cy + qb.z * c.rho.cz;
+        quad_subtriangle<UNIFORM, TABLE>(c.rho, g, P3{qa.x, qa.y, qa.z}, P3{qb.x, qb.y, qb.z}, gc, ac, bc, M0, M1, M2);
         qa = qb;
-        aa = bb;
+        ac = bc;
       }
     }
     const double mm = M0 * M0 + M1 * M1 + M2 * M2;
