@@ -16,6 +16,7 @@ SYMBOLS = [
     "fm_set_generators", "fm_host_alloc", "fm_host_free", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
     "fm_profile_enable", "fm_profile_get", "fm_device_info",
     "fm_fp64_peak", "fm_block_ids", "fm_get_generators_block", "fm_set_generators_block", "fm_quality",
+    "fm_quality_static",
 ]
 
 
@@ -94,5 +95,7 @@ def lib():
         L.fm_set_generators_block.argtypes = [vp, dp, dp, dp]
     if hasattr(L, 'fm_quality'):   # absent from older builds loaded through FM_LIB (A/B runs)
         L.fm_quality.argtypes = [vp, C.POINTER(Density), C.POINTER(QualityStats)]
+    if hasattr(L, 'fm_quality_static'):
+        L.fm_quality_static.argtypes = [vp, C.POINTER(QualityStats)]
     _lib = L
     return L

@@ -5,6 +5,7 @@
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1423,6 +1424,99 @@ extern "C" int fm_quality(fm_handle* h, const fm_density* rho, fm_quality_stats*
   FM_CUDA(cudaMemcpyAsync(host, h->qbuf, sizeof host, cudaMemcpyDeviceToHost, h->stream));
   Readback r;
   if (readback(h, &r, "fm_quality")) return 1;
+  FM_CUDA(cudaMemsetAsync(h->counters + FM_C_MAXDISP, 0, sizeof(u64), h->stream));
+  memcpy(out->degree_hist, host, 16 * sizeof(int64_t));
+  out->area_cell_min = host[16]; out->area_cell_max = host[17];
+  out->area_tri_min = host[18]; out->area_tri_max = host[19];
+  out->angle_min = host[20]; out->angle_max = host[21];
+  out->area_cell_sum = host[22]; out->area_tri_sum = host[23];
+  out->max_disp = r.maxdisp;
+  return 0;
+}
+
+// ---- fm_quality_static: the quality statistics without any allocation (no counterpart in the
+// reference; added for callers that cannot call cudaMalloc:
+// code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+// fm_quality keeps its block partials in a buffer it cudaMallocs on first use (fm_handle::qbuf);
+// here the same 24 header words + 2 * ceil(T / 128) partials live in ONE file-scope device array,
+// sized for FM_QUALITY_STATIC_MAX_GENERATORS generators (2^22: 131,096 doubles = 1.0 MB, held by
+// every GPU that loads the library until the process exits).  All handles and all calls share it
+// and it keeps the last call's contents: the header words are re-initialised by every call, every
+// partial a call reads is written by that call first, so nothing else has to start at zero; calls
+// that overlap on the GPU (two handles = two streams, two host threads) race on it.
+// The array's name in host code is a host-side stand-in, not a device address: the address comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+static const size_t kQualityStaticWords = 24 + 2 * (((size_t)2 * FM_QUALITY_STATIC_MAX_GENERATORS - 4 + 127) / 128);
+static __device__ __align__(256) double fm_quality_static_scratch[kQualityStaticWords];
+
+static const int kMaxDevices = 64;
+static double* g_quality_static_ptr[kMaxDevices] = {nullptr};
+static std::mutex g_quality_static_mu;
+
+// the scratch array's address on the CURRENT device (looked up once per device)
+static cudaError_t quality_static_scratch(int dev, double** out) {
+  std::lock_guard<std::mutex> lock(g_quality_static_mu);
+  if (!g_quality_static_ptr[dev]) {
+    double* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, fm_quality_static_scratch);
+    if (e != cudaSuccess) return e;
+    g_quality_static_ptr[dev] = p;
+  }
+  *out = g_quality_static_ptr[dev];
+  return cudaSuccess;
+}
+
+extern "C" int fm_quality_static(fm_handle* h, fm_quality_stats* out) {
+  if (!out) { h->fail("fm_quality_static: out is null"); return 1; }
+  if (h->n > FM_QUALITY_STATIC_MAX_GENERATORS) {
+    h->fail("fm_quality_static: %d generators exceed the static scratch array's limit of %d (FM_QUALITY_STATIC_MAX_GENERATORS); "
+            "use fm_quality", h->n, (int)FM_QUALITY_STATIC_MAX_GENERATORS);
+    return 1;
+  }
+  if (!h->have_dt) { h->fail("fm_quality_static before fm_triangulate"); return 1; }
+  if (!h->dt_current) {  // a repair may end in a rebuild, whose library calls allocate: not here
+    h->fail("fm_quality_static: the generators moved since the last triangulation; call fm_retriangulate first "
+            "(this entry point allocates nothing and therefore repairs nothing)");
+    return 1;
+  }
+  int dev = -1;
+  FM_CUDA(cudaGetDevice(&dev));
+  cudaPointerAttributes pa;
+  FM_CUDA(cudaPointerGetAttributes(&pa, h->counters));
+  if (dev < 0 || dev >= kMaxDevices || pa.device != dev) {
+    h->fail("fm_quality_static: the handle lives on device %d but device %d is current", pa.device, dev);
+    return 1;
+  }
+  double* scratch = nullptr;
+  FM_CUDA(quality_static_scratch(dev, &scratch));
+  if (!h->have_cc && circumcentres(h, false)) return 1;   // a launch into the arena; no allocation (lonlat = false)
+  const int B = 128;
+  int n = h->n, T = h->n_tri;
+  int nbc = (n + B - 1) / B, nbt = (T + B - 1) / B;
+  if (24 + 2 * (size_t)nbt > kQualityStaticWords) { h->fail("fm_quality_static: internal size check failed"); return 1; }
+  double init[24];
+  memset(init, 0, sizeof init);
+  const double big = 1.0e300;
+  init[16] = big; init[18] = big; init[20] = big;   // minima
+  FM_CUDA(cudaMemcpyAsync(scratch, init, sizeof init, cudaMemcpyHostToDevice, h->stream));
+  QualityCtx q;
+  memset(&q, 0, sizeof q);
+  q.vd = h->vd_ctx(nullptr);
+  q.hist = (unsigned long long*)scratch; q.mm = scratch + 16; q.part = scratch + 24; q.stride = nbt;
+  fm_quality_cells<<<nbc, B, 0, h->stream>>>(q);
+  h->note_cuda(cudaGetLastError(), "quality_cells (static)");
+  fm_quality_triangles<<<nbt, B, 0, h->stream>>>(q);
+  h->note_cuda(cudaGetLastError(), "quality_triangles (static)");
+  fm_sum_partials<<<1, 256, 0, h->stream>>>(q.part, nbc, 0, scratch + 22);
+  fm_sum_partials<<<1, 256, 0, h->stream>>>(q.part + nbt, nbt, 0, scratch + 23);
+  h->n_launch += 4;
+  // the largest generator-to-centroid chord under the uniform density: the Lloyd kernel over all cells, moving nothing
+  FM_CUDA(cudaMemsetAsync(h->counters + FM_C_MAXDISP, 0, sizeof(u64), h->stream));
+  launch_centroid_kernel(h, nullptr, false, true);
+  double host[24];
+  FM_CUDA(cudaMemcpyAsync(host, scratch, sizeof host, cudaMemcpyDeviceToHost, h->stream));
+  Readback r;
+  if (readback(h, &r, "fm_quality_static")) return 1;
   FM_CUDA(cudaMemsetAsync(h->counters + FM_C_MAXDISP, 0, sizeof(u64), h->stream));
   memcpy(out->degree_hist, host, 16 * sizeof(int64_t));
   out->area_cell_min = host[16]; out->area_cell_max = host[17];

@@ -261,6 +261,14 @@ class Mesh:
         self._chk(_lib.lib().fm_quality(self._h, C.byref(rho), C.byref(q)))
         return q.asdict()
 
+    def quality_static(self):
+        """fm_quality_static: the statistics of quality() under the uniform density, computed without
+        any device allocation (scratch in a static device array of the library; at most
+        4,194,304 generators; the triangulation must be current)."""
+        q = _lib.QualityStats()
+        self._chk(_lib.lib().fm_quality_static(self._h, C.byref(q)))
+        return q.asdict()
+
     # ---- Lloyd (SURVEY.md 7.3)
     def lloyd(self, rho=None, max_iter=1, tol=0.0, warm=True):
         rho = rho or density_uniform()

@@ -186,6 +186,22 @@ typedef struct fm_quality_stats {
 } fm_quality_stats;
 int fm_quality(fm_handle* h, const fm_density* rho, fm_quality_stats* out);
 
+/* fm_quality without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same statistics as fm_quality(h, NULL, out) -- uniform
+ * density -- computed by the same kernels; the block partials that fm_quality keeps in a buffer it
+ * allocates on first use live in a file-scope device array of the library instead, sized for
+ * FM_QUALITY_STATIC_MAX_GENERATORS generators (1.0 MB on every GPU that loads the library, until
+ * the process exits).  The call makes no cudaMalloc / cudaFree and no allocating library call.
+ * It fails, with fm_last_error saying why, when the handle holds more generators than the limit,
+ * when the generators moved since the last triangulation (call fm_retriangulate first: this entry
+ * point repairs nothing), or when the handle's device is not the current one.
+ * ALL handles and calls share the one array, and it keeps the previous call's contents (every
+ * call re-initialises what it reads): calls that overlap on the GPU -- two handles, two host
+ * threads -- race on it; serialise them. */
+#define FM_QUALITY_STATIC_MAX_GENERATORS 4194304
+int fm_quality_static(fm_handle* h, fm_quality_stats* out);
+
 /* Page-locked host buffers for the arrays that cross the boundary (optional: any host
  * pointer is accepted, pinned ones copy at full PCIe rate). */
 int fm_host_alloc(size_t bytes, void** out);
