@@ -16,7 +16,7 @@ SYMBOLS = [
     "fm_set_generators", "fm_host_alloc", "fm_host_free", "fm_timer_begin", "fm_timer_end", "fm_stats", "fm_stats_reset",
     "fm_profile_enable", "fm_profile_get", "fm_device_info",
     "fm_fp64_peak", "fm_block_ids", "fm_get_generators_block", "fm_set_generators_block", "fm_quality",
-    "fm_quality_static",
+    "fm_quality_static", "fm_star_stats",
 ]
 
 
@@ -81,6 +81,8 @@ def lib():
     L.fm_timer_begin.argtypes = [vp]
     L.fm_timer_end.argtypes = [vp, dp]
     L.fm_stats.argtypes = [vp, i64p]
+    if hasattr(L, 'fm_star_stats'):
+        L.fm_star_stats.argtypes = [vp, i64p]
     L.fm_stats_reset.argtypes = [vp]
     L.fm_profile_enable.argtypes = [vp, i32]
     L.fm_profile_get.argtypes = [vp, i32, C.c_void_p, i64p, dp, i64p, ip]

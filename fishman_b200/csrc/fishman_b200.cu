@@ -103,6 +103,21 @@ struct fm_handle {
     bool have = false;
   } mp;
   double* qbuf = nullptr;  // fm_quality: 16 histogram words, 6 extrema, 2 sums, then the block partials
+  // cold build by stars (star_kernels.cuh): buffers allocated by the first build that takes that path
+  struct StarBuf {
+    unsigned *key = nullptr, *skey = nullptr, *own = nullptr;
+    int *idx = nullptr, *sidx = nullptr, *colstart = nullptr, *colmid = nullptr, *ring = nullptr, *deg = nullptr, *stri = nullptr;
+    int *listA = nullptr, *listB = nullptr, *listE = nullptr, *listS = nullptr, *sc = nullptr;
+    u64* off = nullptr;
+    P4* spts = nullptr;
+    void* tmp = nullptr;
+    size_t tmp_bytes = 0;
+    int G = 0;
+    bool ready = false, unavailable = false;
+  } star;
+  long long n_star = 0, n_star_fallback = 0;   // cold builds by stars / attempts that fell back to the insertion build
+  double star_irregular = 0.0;                  // fraction of the sampled generators the first pass did not settle cheaply
+  int star_last[8] = {0};                       // the last star build: retried, exact, failed, broken, owned, degree sum, flips of the check, turned-over
   // the density function staged as a table for the Lloyd kernel (Density::tab), for the parameters rho_tab_for
   double* rho_tab = nullptr;
   fm_density rho_tab_for = {};
@@ -595,6 +610,13 @@ extern "C" void fm_destroy(fm_handle* h) {
     for (void* p : mptrs)
       if (p) cudaFree(p);
   }
+  {
+    auto& b = h->star;
+    void* sptrs[] = {b.key, b.skey, b.own, b.idx, b.sidx, b.colstart, b.colmid, b.ring, b.deg, b.stri, b.listA, b.listB, b.listE, b.listS, b.sc,
+                     b.off, b.spts, b.tmp};
+    for (void* p : sptrs)
+      if (p) cudaFree(p);
+  }
   void* ptrs[] = {h->arena, h->bnd, h->ringc, h->orig, h->inv, h->v2t, h->lvl_order, h->prev, h->next_rev, h->rows, h->rankbuf, h->flip_edge,
                   h->role, h->amark, h->listA, h->listB, h->fliplist, h->counters, h->winner, h->vote,
                   h->mailbox, h->scratch64, h->cub_tmp, h->cclon, h->cclat,
@@ -693,23 +715,11 @@ static int sort_triangles(fm_handle* h) {
   return 0;
 }
 
-// cold build: bootstrap + insertion rounds; synchronous
-static int triangulate_cold(fm_handle* h) {
-  CudaBackend be{h};
-  DtCtx c = h->dt_ctx();
-  c.cc = nullptr;  // circumcentres are computed once at the end, not per flip
-  c.ringc = nullptr;  // the ring cache is invalidated as a whole after the build
-  int boot[4];
-  if (dt_bootstrap(be, c, boot, h->errmsg, sizeof h->errmsg)) return 1;
-  fm_init_loc<<<(h->n + 255) / 256, 256, 0, h->stream>>>(h->n, h->loc, boot[0], boot[1], boot[2], boot[3]);
-  h->n_launch++;
-  DtStats st;
-  int rc = dt_run(be, c, h->listA, h->listB, h->lvl_order, h->lvl_off.data(), h->lvl_K, h->prev, boot, &h->stamp, &st,
-                  h->errmsg, sizeof h->errmsg);
-  if (h->cuda_failed || rc) return 1;
-  h->n_tri = c.n_tri;
-  if (h->n_tri != 2 * h->n - 4) { h->fail("triangle count %d != 2N-4", h->n_tri); return 1; }
-  if (sort_triangles(h)) return 1;
+static int repair_async(fm_handle* h, bool sharded = false, bool in_batch = false);
+
+// What follows every cold build, whichever way the rows were made: the ring cache is void, the slot ranges of
+// a sharded mesh are recomputed (slots are sorted by smallest vertex), counters read back.
+static int cold_finish(fm_handle* h, int rounds) {
   if (h->ringc) FM_CUDA(cudaMemsetAsync(h->ringc, 0xff, 32 * (size_t)h->n, h->stream));  // every slot was renumbered
   h->sweep_begin = 0; h->sweep_end = h->n_tri;
   if (h->size > 1) {  // the slots that go with this rank's cells (slots are sorted by smallest vertex now)
@@ -729,11 +739,207 @@ static int triangulate_cold(fm_handle* h) {
   }
   Readback r;
   if (readback(h, &r, "delaunay_triangulation")) return 1;
-  account(h, r, st.rounds);
+  account(h, r, rounds);
   h->n_cold++;
   h->have_dt = true; h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
   h->dt_current = true;
   return 0;
+}
+
+// ---- cold build by stars (star_kernels.cuh).  Returns 0 = built and verified, 1 = refused (the caller runs
+// the insertion build: too few points, FM_COLD_BUILD=flip, a star that did not close, an inconsistency),
+// -1 = CUDA error.  Synchronous.
+static const int kStarMinPoints = 4096;
+static int star_alloc(fm_handle* h) {
+  auto& b = h->star;
+  if (b.ready) return 0;
+  if (b.unavailable) return 1;
+  static const double kappa = getenv("FM_STAR_KAPPA") ? atof(getenv("FM_STAR_KAPPA")) : 1.75;
+  const int n = h->n;
+  const double hh = sqrt(4.0 * 3.14159265358979323846 / n);
+  int G = (int)(2.0 / ((kappa > 0.5 ? kappa : 1.75) * hh));
+  if (G > kStarMaxG) G = kStarMaxG;
+  if (G < 4) { b.unavailable = true; return 1; }
+  b.G = G;
+  size_t sort_bytes = 0, scan_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, b.key, b.skey, b.idx, b.sidx, n, 0, 32, h->stream);
+  cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, b.off, b.off, n + 1, h->stream);
+  b.tmp_bytes = sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
+  bool ok = true;
+  auto A = [&](cudaError_t e) { ok = ok && e == cudaSuccess; };
+  A(dalloc(&b.key, n)); A(dalloc(&b.skey, n)); A(dalloc(&b.own, n)); A(dalloc(&b.idx, n)); A(dalloc(&b.sidx, n));
+  A(dalloc(&b.colstart, (size_t)G * G + 1)); A(dalloc(&b.colmid, (size_t)G * G)); A(dalloc(&b.ring, (size_t)n * kStarCap)); A(dalloc(&b.deg, n));
+  A(dalloc(&b.stri, (size_t)n * kStarCap)); A(dalloc(&b.listA, n)); A(dalloc(&b.listB, n)); A(dalloc(&b.listE, n)); A(dalloc(&b.listS, n));
+  A(dalloc(&b.sc, 8)); A(dalloc(&b.off, (size_t)n + 1)); A(dalloc(&b.spts, n)); A(cudaMalloc(&b.tmp, b.tmp_bytes));
+  if (ok) {
+    A(cudaMemsetAsync(b.ring, 0, sizeof(int) * (size_t)n * kStarCap, h->stream));
+    A(cudaMemsetAsync(b.stri, 0, sizeof(int) * (size_t)n * kStarCap, h->stream));
+    A(cudaMemsetAsync(b.deg, 0, sizeof(int) * (size_t)n, h->stream));
+  }
+  if (!ok) {  // not enough memory for the ~300 bytes per generator: the insertion build needs none of it
+    cudaGetLastError();
+    void* sptrs[] = {b.key, b.skey, b.own, b.idx, b.sidx, b.colstart, b.colmid, b.ring, b.deg, b.stri, b.listA, b.listB, b.listE, b.listS, b.sc,
+                     b.off, b.spts, b.tmp};
+    for (void* p : sptrs)
+      if (p) cudaFree(p);
+    b = fm_handle::StarBuf();
+    b.unavailable = true;
+    return 1;
+  }
+  {  // the widest retry pass wants more than the default 48 KB of dynamic shared memory
+    const int want = (int)(sizeof(int) * (2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) + 4 * kStarList) * FM_STAR_BLOCK);
+    if (cudaFuncSetAttribute(fm_star_retry, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
+        cudaFuncSetAttribute(fm_star_slow, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
+        cudaFuncSetAttribute(fm_star_exact, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess) {
+      cudaGetLastError();
+      b.unavailable = true;
+      return 1;
+    }
+  }
+  b.ready = true;
+  return 0;
+}
+
+static int triangulate_star(fm_handle* h) {
+  const char* mode = getenv("FM_COLD_BUILD");   // read at every build: the tests switch between the two
+  const bool off = mode && !strcmp(mode, "flip");
+  if (off || h->n < kStarMinPoints) return 1;
+  if (star_alloc(h)) return 1;
+#define S(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->cuda_failed = true; \
+    h->fail("CUDA error %s at %s:%d", cudaGetErrorString(e_), __FILE__, __LINE__); return -1; } } while (0)
+  auto& b = h->star;
+  const int n = h->n, T = 2 * n - 4, G = b.G;
+  StarCtx s;
+  memset(&s, 0, sizeof s);
+  s.n = n; s.G = G; s.half_g = 0.5 * G; s.cell = 2.0 / G;
+  s.pts = h->pts; s.key = b.key; s.idx = b.idx; s.skey = b.skey; s.sidx = b.sidx; s.spts = b.spts; s.colstart = b.colstart; s.colmid = b.colmid;
+  s.ring = b.ring; s.deg = b.deg; s.own = b.own; s.off = b.off; s.stri = b.stri;
+  s.list_exact = b.listE; s.list_slow = b.listS; s.sc = b.sc; s.row = h->rows; s.v2t = h->v2t;
+  const int nb = (n + 255) / 256;
+  cudaStream_t st = h->stream;
+  // 1. grid: keys, sort by cell, records in sorted order, column starts
+  h->prof_begin();
+  S(cudaMemsetAsync(b.sc, 0, 8 * sizeof(int), st));
+  fm_star_kernel<KStarKey><<<nb, 256, 0, st>>>(s, n);
+  int bits = 1;
+  while ((1ULL << bits) < (unsigned long long)G * G * G) bits++;
+  size_t bytes = b.tmp_bytes;
+  S(cub::DeviceRadixSort::SortPairs(b.tmp, bytes, b.key, b.skey, b.idx, b.sidx, n, 0, bits, st));
+  fm_star_kernel<KStarGather><<<nb, 256, 0, st>>>(s, n);
+  fm_star_kernel<KStarCols><<<(G * G + 1 + 255) / 256, 256, 0, st>>>(s, G * G + 1);
+  h->prof_end("star_grid", n);
+  // 2. stars: all generators with a block of radius 1, then the ones that need more / the exact predicates
+  int* lists[2] = {b.listA, b.listB};
+  auto smem = [](int r) { return sizeof(int) * (2 * (2 * r + 1) * (2 * r + 1) + 4 * kStarList) * FM_STAR_BLOCK; };
+  const size_t smem_full = sizeof(int) * 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) * FM_STAR_BLOCK;
+  {
+    static const double near_h = getenv("FM_STAR_NEAR") ? atof(getenv("FM_STAR_NEAR")) : 1.5;
+    s.near2 = near_h * near_h * 4.0 * 3.14159265358979323846 / n;
+  }
+  s.r = 1; s.cap_all = star_cap_all(1); s.in_idx = 1; s.out_idx = 0; s.list_out = lists[0]; s.list_in = lists[1];
+  {  // Is this point set one the stars are good at?  1/64 of the generators (whole blocks, so that the lanes of a
+     // warp are neighbours as in the real pass) go through the first pass without recording anything: where more
+     // than a tenth of them need the full wrap, a wider block or three rounds of the near list (uniform random
+     // points do), the insertion build is the faster one.
+    static const double max_frac = getenv("FM_STAR_MAX_IRREGULAR") ? atof(getenv("FM_STAR_MAX_IRREGULAR")) : 0.10;
+    const int every = 64, nblk = (n + FM_STAR_BLOCK - 1) / FM_STAR_BLOCK, sblk = (nblk + every - 1) / every;
+    s.dry = 1;
+    h->prof_begin();
+    fm_star_sample<<<sblk, FM_STAR_BLOCK, smem(1), st>>>(s, n, every);
+    h->prof_end("star_sample", sblk * FM_STAR_BLOCK);
+    s.dry = 0;
+    int sc0[8];
+    S(cudaMemcpyAsync(sc0, b.sc, sizeof sc0, cudaMemcpyDeviceToHost, st));
+    S(h->sync());
+    S(cudaMemsetAsync(b.sc, 0, 8 * sizeof(int), st));
+    h->n_launch++;
+    const double frac = (double)(sc0[FM_SC_RETRIED] + sc0[FM_SC_MULTI]) / ((double)sblk * FM_STAR_BLOCK);
+    h->star_irregular = frac;
+    if (frac > max_frac) { h->n_star_fallback++; h->star_last[2] = -1; return 1; }
+  }
+  h->prof_begin();
+  fm_star_all<<<(n + FM_STAR_BLOCK - 1) / FM_STAR_BLOCK, FM_STAR_BLOCK, smem(1), st>>>(s, n);
+  h->prof_end("star_wrap", n);
+  h->prof_begin();
+  for (int r = 2; r <= kStarMaxR; r++) {
+    s.r = r; s.cap_all = star_cap_all(r); s.in_idx = (r & 1) ? 1 : 0; s.out_idx = s.in_idx ^ 1;
+    s.list_in = lists[s.in_idx]; s.list_out = lists[s.out_idx];
+    S(cudaMemsetAsync(b.sc + s.out_idx, 0, sizeof(int), st));
+    fm_star_retry<<<h->sms * 8, FM_STAR_BLOCK, smem(r), st>>>(s);
+  }
+  fm_star_slow<<<h->sms * 8, FM_STAR_BLOCK, smem_full, st>>>(s);
+  fm_star_exact<<<h->sms * 8, FM_STAR_BLOCK, smem_full, st>>>(s);
+  h->prof_end("star_retry", 0);
+  // 3. rows
+  h->prof_begin();
+  fm_star_kernel<KStarOwn><<<nb, 256, 0, st>>>(s, n);
+  bytes = b.tmp_bytes;
+  S(cub::DeviceScan::ExclusiveSum(b.tmp, bytes, b.off, b.off, n + 1, st));
+  fm_star_kernel<KStarSlots><<<nb, 256, 0, st>>>(s, n);
+  fm_star_kernel<KStarRows><<<nb, 256, 0, st>>>(s, n);
+  h->prof_end("star_rows", n);
+  h->n_launch += 12 + (kStarMaxR - 1);
+  S(cudaGetLastError());
+  int sc[8];
+  u64 tot = 0;
+  S(cudaMemcpyAsync(sc, b.sc, sizeof sc, cudaMemcpyDeviceToHost, st));
+  S(cudaMemcpyAsync(&tot, b.off + n, sizeof tot, cudaMemcpyDeviceToHost, st));
+  S(h->sync());
+  const int owned = (int)(tot & 0xffffffffULL), degsum = (int)(tot >> 32);
+  h->star_last[0] = sc[FM_SC_SLOW]; h->star_last[1] = sc[FM_SC_EXACT]; h->star_last[2] = sc[FM_SC_FAIL]; h->star_last[3] = sc[FM_SC_BROKEN];
+  h->star_last[4] = owned; h->star_last[5] = degsum; h->star_last[6] = 0; h->star_last[7] = 0;
+  if (sc[FM_SC_FAIL] || sc[FM_SC_BROKEN] || owned != T || degsum != 3 * T) {   // the rows are rewritten by the insertion build
+    h->n_star_fallback++;
+    return 1;
+  }
+  h->n_tri = T;
+  S(cudaMemsetAsync(h->role, 0, sizeof(int) * (size_t)T, st));
+  S(cudaMemsetAsync(h->amark, 0, sizeof(int) * (size_t)T, st));
+  // 4. the check: orientation of every triangle and the local Delaunay test of every edge (the warm sweep;
+  // it also writes the circumcentres).  A consistent closed surface that passes is THE triangulation.
+  fm_bump_stamp<<<1, 1, 0, st>>>(h->counters, 2);
+  h->have_dt = true;
+  if (h->ringc) S(cudaMemsetAsync(h->ringc, 0xff, 32 * (size_t)n, st));
+  h->sweep_begin = 0; h->sweep_end = T;
+  if (repair_async(h)) return -1;
+  Readback r;
+  if (readback(h, &r, "delaunay_triangulation (stars)")) return -1;
+  h->star_last[6] = r.counters[2]; h->star_last[7] = r.counters[3];
+  if (r.counters[3] > 0 || r.counters[2] > 0) {   // never seen; the insertion build starts from scratch
+    h->n_star_fallback++;
+    h->have_dt = false;
+    return 1;
+  }
+  h->n_star++;
+  if (cold_finish(h, 0)) return -1;
+  h->have_cc = true;   // written by the sweep
+  return 0;
+#undef S
+}
+
+// cold build: by stars when the generators allow it (star_kernels.cuh), else bootstrap + insertion rounds; synchronous
+static int triangulate_cold(fm_handle* h) {
+  {
+    int rc = triangulate_star(h);
+    if (rc == 0) return 0;
+    if (rc < 0) return 1;   // a CUDA error, not a refusal
+  }
+  CudaBackend be{h};
+  DtCtx c = h->dt_ctx();
+  c.cc = nullptr;  // circumcentres are computed once at the end, not per flip
+  c.ringc = nullptr;  // the ring cache is invalidated as a whole after the build
+  int boot[4];
+  if (dt_bootstrap(be, c, boot, h->errmsg, sizeof h->errmsg)) return 1;
+  fm_init_loc<<<(h->n + 255) / 256, 256, 0, h->stream>>>(h->n, h->loc, boot[0], boot[1], boot[2], boot[3]);
+  h->n_launch++;
+  DtStats st;
+  int rc = dt_run(be, c, h->listA, h->listB, h->lvl_order, h->lvl_off.data(), h->lvl_K, h->prev, boot, &h->stamp, &st,
+                  h->errmsg, sizeof h->errmsg);
+  if (h->cuda_failed || rc) return 1;
+  h->n_tri = c.n_tri;
+  if (h->n_tri != 2 * h->n - 4) { h->fail("triangle count %d != 2N-4", h->n_tri); return 1; }
+  if (sort_triangles(h)) return 1;
+  return cold_finish(h, st.rounds);
 }
 
 // warm repair of the existing connectivity, launches only; the caller reads counters[3]
@@ -741,7 +947,7 @@ static void launch_peer_barrier(fm_handle* h, int phase);
 // sharded: (Lloyd loop on a mesh with attached peers) each rank sweeps its own triangle slots and
 // sends what it finds to all ranks; barrier; every rank applies all requests and runs the same
 // flip rounds.  Every rank must call this in step.
-static int repair_async(fm_handle* h, bool sharded = false, bool in_batch = false) {
+static int repair_async(fm_handle* h, bool sharded, bool in_batch) {
   CudaBackend be{h};
   be.in_batch = in_batch;
   DtCtx c = h->dt_ctx();
@@ -1684,13 +1890,19 @@ extern "C" int fm_timer_end(fm_handle* h, double* ms) {
 
 extern "C" int fm_stats(const fm_handle* h, int64_t* s) {
   s[0] = h->tot_rounds; s[1] = h->tot_sub; s[2] = h->tot_flips; s[3] = h->max_active;
-  s[4] = h->n_launch; s[5] = h->n_cold; s[6] = h->n_warm; s[7] = 0;
+  s[4] = h->n_launch; s[5] = h->n_cold; s[6] = h->n_warm; s[7] = h->n_star;
+  return 0;
+}
+extern "C" int fm_star_stats(const fm_handle* h, int64_t* out) {
+  out[0] = h->n_star; out[1] = h->n_star_fallback;
+  for (int k = 0; k < 8; k++) out[2 + k] = h->star_last[k];
   return 0;
 }
 extern "C" int fm_stats_reset(fm_handle* h) {
   h->tot_rounds = h->tot_sub = h->tot_flips = 0;
   h->max_active = 0;
   h->n_launch = h->n_cold = h->n_warm = 0;
+  h->n_star = h->n_star_fallback = 0;
   h->sync();
   h->prof.clear();
   return 0;

@@ -7,6 +7,7 @@
 
 #include "dt_driver.h"
 #include "vd_kernels.cuh"
+#include "star_kernels.cuh"
 
 namespace fm {
 namespace cg = cooperative_groups;
@@ -198,6 +199,48 @@ __global__ void __launch_bounds__(256) fm_flip_coop(DtCtx c, int* listA, int* li
     c.counters[5] += sub;
     if (maxq > c.counters[6]) c.counters[6] = maxq;
   }
+}
+
+// ---- cold build by stars (star_kernels.cuh)
+template <class K>
+__global__ void __launch_bounds__(256) fm_star_kernel(StarCtx s, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) K::run(s, i);
+}
+// The wrap kernels: 64 threads per block, 2 (2r+1)^2 ints of shared memory per thread (the candidate
+// ranges of the block of cells).  Threads are in SORTED order: the lanes of a warp are neighbours on
+// the sphere and read the same few cells' records through L1.
+#ifndef FM_STAR_BLOCK
+#define FM_STAR_BLOCK 64
+#endif
+__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_all(StarCtx s, int n) {
+  extern __shared__ int star_smem[];
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) KStarAllT<false>::run(s, j, star_smem + threadIdx.x, blockDim.x);
+}
+// the sampling pass (StarCtx::dry): the first block of every `every` blocks
+__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_sample(StarCtx s, int n, int every) {
+  extern __shared__ int star_smem[];
+  int j = blockIdx.x * every * blockDim.x + threadIdx.x;
+  if (j < n) KStarAllT<false>::run(s, j, star_smem + threadIdx.x, blockDim.x);
+}
+__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_retry(StarCtx s) {
+  extern __shared__ int star_smem[];
+  const int m = s.sc[s.in_idx];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
+    KStarRetry::run(s, i, star_smem + threadIdx.x, blockDim.x);
+}
+__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_slow(StarCtx s) {
+  extern __shared__ int star_smem[];
+  const int m = s.sc[FM_SC_SLOW];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
+    KStarSlow::run(s, i, star_smem + threadIdx.x, blockDim.x);
+}
+__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_exact(StarCtx s) {
+  extern __shared__ int star_smem[];
+  const int m = s.sc[FM_SC_EXACT];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
+    KStarExact::run(s, i, star_smem + threadIdx.x, blockDim.x);
 }
 
 __global__ void fm_bump_stamp(int* counters, int by) { counters[FM_C_STAMP] += by; }

@@ -261,6 +261,15 @@ class Mesh:
         self._chk(_lib.lib().fm_quality(self._h, C.byref(rho), C.byref(q)))
         return q.asdict()
 
+    def star_stats(self):
+        """fm_star_stats: dict about the cold builds by stars (csrc/star_kernels.cuh)."""
+        import numpy as np
+        out = np.zeros(10, np.int64)
+        self._chk(_lib.lib().fm_star_stats(self._h, out.ctypes.data_as(C.POINTER(C.c_int64))))
+        names = ("builds", "fallbacks", "reserved", "exact", "failed", "broken", "triangles", "degree_sum", "check_flips",
+                 "check_turned")
+        return dict(zip(names, (int(v) for v in out)))
+
     def quality_static(self):
         """fm_quality_static: the statistics of quality() under the uniform density, computed without
         any device allocation (scratch in a static device array of the library; at most

@@ -99,3 +99,21 @@ def rebuild_after_failed_repair(xyz_old, xyz_new, skip_bump=False):
     if rc:
         raise RuntimeError(lib().fme_last_error().decode())
     return tri, adj, turned.value
+
+
+def triangulate_star(xyz, kappa=1.5):
+    """Cold build by stars (csrc/star_kernels.cuh) on the host.  Returns (rc, tri, adj, stats): rc 0 = complete,
+    2 = the product would fall back to the insertion build (stats say why)."""
+    p = np.ascontiguousarray(xyz, dtype=np.float64)
+    n = len(p)
+    T = 2 * n - 4
+    tri = np.zeros((T, 3), np.int32)
+    adj = np.zeros((T, 3), np.int32)
+    st = np.zeros(8, np.int32)
+    ip = C.POINTER(C.c_int)
+    rc = lib().fme_triangulate_star(n, p.ctypes.data_as(C.POINTER(C.c_double)), C.c_double(kappa),
+                                    tri.ctypes.data_as(ip), adj.ctypes.data_as(ip), st.ctypes.data_as(ip))
+    if rc == 1:
+        raise RuntimeError(lib().fme_last_error().decode())
+    names = ("retried", "exact", "failed", "broken", "owned", "degree_sum", "cells_per_axis", "slow")
+    return rc, tri, adj, dict(zip(names, (int(v) for v in st[:8])))

@@ -270,3 +270,88 @@ extern "C" int fme_rebuild_after_failed_repair(int n, const double* xyz_old, con
   m.export_tris(tri_out, adj_out);
   return 0;
 }
+
+// ---- cold build by stars (csrc/star_kernels.cuh) on the host: grid, stars, rows.
+// stats: [0] generators retried with a wider block, [1] generators redone with exact predicates,
+// [2] stars that failed, [3] triangles not found in their owner's star, [4] owned triangles, [5] sum of degrees,
+// [6] cells per axis.  Returns 0 when the build is complete and consistent, 2 when the product would
+// fall back to the insertion build, 1 on a usage error.
+#include "../../fishman_b200/csrc/star_kernels.cuh"
+
+extern "C" int fme_triangulate_star(int n, const double* xyz, double kappa, int* tri_out, int* adj_out, int* stats) {
+  g_err[0] = 0;
+  if (n < 16) { snprintf(g_err, sizeof g_err, "need at least 16 points"); return 1; }
+  const int T = 2 * n - 4;
+  std::vector<int> orig(n);
+  std::iota(orig.begin(), orig.end(), 0);
+  {
+    std::vector<u64> key(n);
+    for (int i = 0; i < n; i++) key[i] = morton_key(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+    std::stable_sort(orig.begin(), orig.end(), [&](int a, int b) { return key[a] < key[b]; });
+  }
+  std::vector<P4> pts(n), spts(n);
+  for (int i = 0; i < n; i++) pts[i] = P4{xyz[3 * orig[i]], xyz[3 * orig[i] + 1], xyz[3 * orig[i] + 2], orig[i]};
+  StarCtx s;
+  memset(&s, 0, sizeof s);
+  const double h = sqrt(4.0 * 3.14159265358979323846 / n);
+  int G = (int)(2.0 / (kappa * h));
+  if (G < 1) G = 1;
+  if (G > kStarMaxG) G = kStarMaxG;
+  s.n = n; s.G = G; s.half_g = 0.5 * G; s.cell = 2.0 / G;
+  std::vector<unsigned> key(n), skey(n);
+  std::vector<int> idx(n), sidx(n), colstart((size_t)G * G + 1), colmid((size_t)G * G), ring((size_t)n * kStarCap, 0), deg(n, 0),
+      stri((size_t)n * kStarCap, 0), listA(n), listB(n), listE(n), listS(n), v2t(n, -1);
+  std::vector<unsigned> own(n, 0);
+  std::vector<u64> off(n + 1, 0);
+  std::vector<Row> row(T);
+  int sc[8] = {0};
+  s.pts = pts.data(); s.key = key.data(); s.idx = idx.data();
+  for (int i = 0; i < n; i++) KStarKey::run(s, i);
+  std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return key[a] < key[b]; });
+  for (int j = 0; j < n; j++) { sidx[j] = idx[j]; skey[j] = key[idx[j]]; }
+  s.skey = skey.data(); s.sidx = sidx.data(); s.spts = spts.data(); s.colstart = colstart.data(); s.colmid = colmid.data();
+  for (int j = 0; j < n; j++) KStarGather::run(s, j);
+  for (int c = 0; c <= G * G; c++) KStarCols::run(s, c);
+  s.ring = ring.data(); s.deg = deg.data(); s.own = own.data(); s.off = off.data(); s.stri = stri.data();
+  s.list_exact = listE.data(); s.list_slow = listS.data(); s.sc = sc; s.row = row.data(); s.v2t = v2t.data();
+  std::vector<int> rng(4 * kStarList + 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1));
+  s.near2 = 2.25 * h * h;
+  int* lists[2] = {listA.data(), listB.data()};
+  s.r = 1; s.cap_all = star_cap_all(1); s.in_idx = 1; s.out_idx = 0; s.list_out = lists[0];
+  for (int j = 0; j < n; j++) KStarAllT<false>::run(s, j, rng.data(), 1);
+  int retried = sc[0];
+  for (int r = 2; r <= kStarMaxR; r++) {
+    s.r = r; s.cap_all = star_cap_all(r); s.in_idx = (r & 1) ? 1 : 0; s.out_idx = s.in_idx ^ 1;
+    s.list_in = lists[s.in_idx]; s.list_out = lists[s.out_idx];
+    sc[s.out_idx] = 0;
+    for (int i = 0, m = sc[s.in_idx]; i < m; i++) KStarRetry::run(s, i, rng.data(), 1);
+  }
+  for (int i = 0, m = sc[FM_SC_SLOW]; i < m; i++) KStarSlow::run(s, i, rng.data(), 1);
+  for (int i = 0, m = sc[FM_SC_EXACT]; i < m; i++) KStarExact::run(s, i, rng.data(), 1);
+  for (int i = 0; i < n; i++) KStarOwn::run(s, i);
+  {
+    u64 acc = 0;
+    for (int i = 0; i <= n; i++) { u64 v = off[i]; off[i] = acc; acc += v; }
+  }
+  const int owned = (int)(off[n] & 0xffffffffULL), degsum = (int)(off[n] >> 32);
+  if (stats) {
+    stats[0] = retried; stats[7] = sc[FM_SC_SLOW]; stats[1] = sc[FM_SC_EXACT]; stats[2] = sc[FM_SC_FAIL]; stats[4] = owned; stats[5] = degsum; stats[6] = G;
+  }
+  if (sc[FM_SC_FAIL] || owned != T || degsum != 3 * T) {
+    if (stats) stats[3] = -1;
+    snprintf(g_err, sizeof g_err, "stars incomplete: %d failed, %d owned triangles (want %d), degree sum %d (want %d)",
+             sc[FM_SC_FAIL], owned, T, degsum, 3 * T);
+    return 2;
+  }
+  for (int i = 0; i < n; i++) KStarSlots::run(s, i);
+  if (!sc[FM_SC_BROKEN])
+    for (int i = 0; i < n; i++) KStarRows::run(s, i);
+  if (stats) stats[3] = sc[FM_SC_BROKEN];
+  if (sc[FM_SC_BROKEN]) { snprintf(g_err, sizeof g_err, "stars inconsistent: %d triangles", sc[FM_SC_BROKEN]); return 2; }
+  for (int t = 0; t < T; t++)
+    for (int k = 0; k < 3; k++) {
+      tri_out[3 * t + k] = orig[geti(row[t].v, k)] + 1;
+      adj_out[3 * t + k] = (geti(row[t].a, k) >> 2) + 1;
+    }
+  return 0;
+}

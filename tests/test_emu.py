@@ -163,3 +163,47 @@ def test_rebuild_after_a_failed_warm_repair(n):
             differ_without += 1
     if n == 40:
         assert differ_without > 0   # the defect is real: without the bump some rebuilds are not Delaunay
+
+
+# ---- cold build by stars (csrc/star_kernels.cuh), kernel bodies on the host
+def _star_sets():
+    from fishman_b200 import points
+    return [("fib5000", points.fibonacci(5000, 0)), ("fib20000_nojitter", points.fibonacci(20000, 0, 0.0)),
+            ("u6000", points.uniform(6000, 3)), ("ico4", points.ico(4)), ("ico5", points.ico(5))]
+
+
+@pytest.mark.parametrize("name", [s[0] for s in _star_sets()])
+@pytest.mark.parametrize("kappa", [1.5, 2.0, 3.0])
+def test_star_build_equals_insertion_build(name, kappa):
+    """Every generator's star found independently (grid, gift wrapping with the filtered / exact predicates,
+    fp32 guess + certificate) gives the triangulation the insertion + flip rounds give, triangle for triangle
+    (both are the Delaunay triangulation of the SoS-perturbed points), whatever the cell size; rows and
+    adjacency are a valid closed triangulation."""
+    from tests import _check
+    p = dict(_star_sets())[name]
+    rc, tri, adj, st = _emu.triangulate_star(p, kappa)
+    assert rc == 0, st
+    assert st["failed"] == 0 and st["broken"] == 0 and st["owned"] == 2 * len(p) - 4 and st["degree_sum"] == 6 * len(p) - 12
+    _check.check_triangulation(p, tri, adj)
+    t2, _, _ = _emu.triangulate(p)
+    assert np.array_equal(_check.canonical(tri), _check.canonical(t2))
+
+
+def test_star_build_refuses_what_it_cannot_do():
+    """A lat-lon grid (poles of degree nlon, rows of cocircular points) and a clustered set: stars that do not close
+    within kStarCap neighbours / kStarMaxR cells are reported, never a wrong triangulation: rc 2 = the product
+    runs the insertion build."""
+    from fishman_b200 import points
+    p = points.latlon_grid(40, 80)
+    rc, tri, adj, st = _emu.triangulate_star(p, 2.0)
+    assert rc == 2 and (st["failed"] > 0 or st["broken"] != 0)
+    rng = np.random.default_rng(0)
+    q = np.concatenate([points.uniform(3000, 1), points.uniform(3000, 2) * 1e-3 + np.array([0, 0, 1.0])])
+    q /= np.linalg.norm(q, axis=1)[:, None]
+    rc, tri, adj, st = _emu.triangulate_star(q, 2.0)
+    if rc == 0:   # allowed to succeed -- then it must be right
+        from tests import _check
+        t2, _, _ = _emu.triangulate(q)
+        assert np.array_equal(_check.canonical(tri), _check.canonical(t2))
+    else:
+        assert rc == 2

@@ -392,3 +392,51 @@ def test_block_transfer_single_rank(fb):
     assert np.array_equal(m.generators(), q)
     m.delaunay_triangulation()
     m.close()
+
+
+@pytest.mark.parametrize("name", ["fib60000", "fib60000_nojitter", "ico6", "u50000", "latlon"])
+def test_cold_build_by_stars_equals_insertion_build(fb, name):
+    """The cold build by stars (csrc/star_kernels.cuh) against the insertion + flip rounds on the same handle
+    (FM_COLD_BUILD=flip switches the stars off): identical triangles; the stars' verifying sweep finds nothing
+    to flip; sets the stars are not made for (uniform random points: too many wide searches; a lat-lon grid:
+    poles of degree nlon) are refused and built by insertion -- same answer, by the other path."""
+    import os
+    from fishman_b200 import points
+    p = {"fib60000": lambda: points.fibonacci(60000, 4), "fib60000_nojitter": lambda: points.fibonacci(60000, 0, 0.0),
+         "ico6": lambda: points.ico(6), "u50000": lambda: points.uniform(50000, 7),
+         "latlon": lambda: points.latlon_grid(100, 200)}[name]()
+    m = fb.Mesh.from_xyz(p)
+    old = os.environ.pop("FM_COLD_BUILD", None)
+    try:
+        m.stats_reset()
+        m.delaunay_triangulation()
+        st = m.star_stats()
+        tri, adj = m.triangles()
+        _check.check_triangulation(p, tri, adj)
+        if name in ("u50000", "latlon"):
+            assert st["builds"] == 0 and st["fallbacks"] == 1
+        else:
+            assert st["builds"] == 1 and st["fallbacks"] == 0 and st["failed"] == 0 and st["broken"] == 0
+            assert st["triangles"] == 2 * len(p) - 4 and st["degree_sum"] == 6 * len(p) - 12
+            assert st["check_flips"] == 0 and st["check_turned"] == 0
+        os.environ["FM_COLD_BUILD"] = "flip"
+        m.stats_reset()
+        m.retriangulate(warm=False)
+        assert m.star_stats()["builds"] == 0
+        tri2, adj2 = m.triangles()
+        assert np.array_equal(_check.canonical(tri), _check.canonical(tri2))
+        # a Lloyd run through both: the generators agree to the last bit or two (the slot order differs, and with it
+        # the order of the sums)
+        g_flip = None
+        m.lloyd(max_iter=3, warm=True)
+        g_flip = m.generators()
+        del os.environ["FM_COLD_BUILD"]
+        m2 = fb.Mesh.from_xyz(p)
+        m2.lloyd(max_iter=3, warm=True)
+        assert np.abs(m2.generators() - g_flip).max() < TOL
+        m2.close()
+    finally:
+        os.environ.pop("FM_COLD_BUILD", None)
+        if old is not None:
+            os.environ["FM_COLD_BUILD"] = old
+        m.close()

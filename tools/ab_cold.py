@@ -20,4 +20,5 @@ rows = sorted(m.profile_rows(), key=lambda r: -r["ms"])
 m.profile(False)
 print(json.dumps({"lib": os.environ.get("FM_LIB", "in-tree"), "n": n, "kind": kind, "ms": float(np.median(ts)), "all": ts,
                   "Mpts_s": n / np.median(ts) / 1e3,
-                  "kernels": [(r["name"], r["launches"], round(r["ms"], 3)) for r in rows[:12]]}))
+                  "kernels": [(r["name"], r["launches"], round(r["ms"], 3)) for r in rows[:12]],
+                  "star": m.star_stats() if hasattr(m, "star_stats") else None}))
