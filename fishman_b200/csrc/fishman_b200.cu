@@ -754,10 +754,10 @@ static int star_alloc(fm_handle* h) {
   auto& b = h->star;
   if (b.ready) return 0;
   if (b.unavailable) return 1;
-  static const double kappa = getenv("FM_STAR_KAPPA") ? atof(getenv("FM_STAR_KAPPA")) : 1.75;
+  static const double kappa = getenv("FM_STAR_KAPPA") ? atof(getenv("FM_STAR_KAPPA")) : 2.0;
   const int n = h->n;
   const double hh = sqrt(4.0 * 3.14159265358979323846 / n);
-  int G = (int)(2.0 / ((kappa > 0.5 ? kappa : 1.75) * hh));
+  int G = (int)(2.0 / ((kappa > 0.5 ? kappa : 2.0) * hh));
   if (G > kStarMaxG) G = kStarMaxG;
   if (G < 4) { b.unavailable = true; return 1; }
   b.G = G;
@@ -833,8 +833,8 @@ static int triangulate_star(fm_handle* h) {
   auto smem = [](int r) { return sizeof(int) * (2 * (2 * r + 1) * (2 * r + 1) + 4 * kStarList) * FM_STAR_BLOCK; };
   const size_t smem_full = sizeof(int) * 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) * FM_STAR_BLOCK;
   {
-    static const double near_h = getenv("FM_STAR_NEAR") ? atof(getenv("FM_STAR_NEAR")) : 1.5;
-    s.near2 = near_h * near_h * 4.0 * 3.14159265358979323846 / n;
+    static const double near_scale = getenv("FM_STAR_NEAR") ? atof(getenv("FM_STAR_NEAR")) : 1.0;
+    s.near2 = near_scale > 0.0 ? near_scale : 1.0;
   }
   s.r = 1; s.cap_all = star_cap_all(1); s.in_idx = 1; s.out_idx = 0; s.list_out = lists[0]; s.list_in = lists[1];
   {  // Is this point set one the stars are good at?  1/64 of the generators (whole blocks, so that the lanes of a
@@ -865,14 +865,14 @@ static int triangulate_star(fm_handle* h) {
     s.r = r; s.cap_all = star_cap_all(r); s.in_idx = (r & 1) ? 1 : 0; s.out_idx = s.in_idx ^ 1;
     s.list_in = lists[s.in_idx]; s.list_out = lists[s.out_idx];
     S(cudaMemsetAsync(b.sc + s.out_idx, 0, sizeof(int), st));
-    fm_star_retry<<<h->sms * 8, FM_STAR_BLOCK, smem(r), st>>>(s);
+    fm_star_retry<<<h->sms * (r == 2 ? 4 : 1), FM_STAR_BLOCK, smem(r), st>>>(s);   // (few generators get here: a small grid starts and ends quickly)
   }
-  fm_star_slow<<<h->sms * 8, FM_STAR_BLOCK, smem_full, st>>>(s);
-  fm_star_exact<<<h->sms * 8, FM_STAR_BLOCK, smem_full, st>>>(s);
+  fm_star_slow<<<h->sms * 2, FM_STAR_BLOCK, smem_full, st>>>(s);
+  fm_star_exact<<<h->sms * 2, FM_STAR_BLOCK, smem_full, st>>>(s);
   h->prof_end("star_retry", 0);
   // 3. rows
   h->prof_begin();
-  fm_star_kernel<KStarOwn><<<nb, 256, 0, st>>>(s, n);
+  S(cudaMemsetAsync(b.off + n, 0, sizeof(u64), st));
   bytes = b.tmp_bytes;
   S(cub::DeviceScan::ExclusiveSum(b.tmp, bytes, b.off, b.off, n + 1, st));
   fm_star_kernel<KStarSlots><<<nb, 256, 0, st>>>(s, n);

@@ -40,7 +40,10 @@ namespace fm {
 static const int kStarCap = 24;   // ring slots per generator (fixed stride: 96 bytes = 3 sectors)
 static const int kStarMaxR = 4;   // widest block searched: (2 * 4 + 1)^3 cells
 static const int kStarMaxG = 1600;  // cells per axis: G^3 < 2^32 (32-bit cell keys)
-static const int kStarList = 32;  // near candidates per generator kept by the filter kernels (wrap_near)
+#ifndef FM_STAR_LIST
+#define FM_STAR_LIST 16
+#endif
+static const int kStarList = FM_STAR_LIST;  // near candidates per generator kept by the filter kernels (wrap_near)
 // capacity of wrap_near's flat candidate list for a block of radius r (a block holds ~ (2r+1)^2 kappa^2 generators)
 FM_HD inline int star_cap_all(int r) { return r <= 1 ? 64 : (r == 2 ? 160 : (r == 3 ? 320 : 512)); }
 enum { FM_S_OK = 0, FM_S_RADIUS = 1, FM_S_UNSURE = 2, FM_S_FAIL = 3, FM_S_SLOW = 4 };
@@ -70,7 +73,7 @@ struct StarCtx {
   int r;                 // block radius of this pass (cells)
   int dry;               // sampling pass: statuses are only counted (sc[FM_SC_RETRIED] not OK, sc[FM_SC_MULTI] OK after >= 3 rounds)
   int cap_all;           // capacity of wrap_near's flat candidate list in this pass
-  double near2;          // first near-list radius, squared (1.5 mean spacings)
+  double near2;          // scale of the first near-list radius, squared (1 = ~7.5 expected entries)
   int in_idx, out_idx;   // which of sc[0], sc[1] counts list_in / list_out
   Row* row;
   int* v2t;
@@ -119,6 +122,29 @@ struct KStarCols {   // over G * G + 1 columns
 #define FM_STAR_FOR(q)                        \
   for (int a_ = 0; a_ < nr; a_++)             \
     for (int q = rng[(2 * a_) * stride], e_ = rng[(2 * a_ + 1) * stride]; q < e_; q++)
+
+// A star is complete: its length, which of its triangles the generator owns (it is their smallest vertex), and the
+// (owned count | degree << 32) word the scan turns into slot offsets.  The ring was just written by this thread.
+FM_HD inline int star_popc(unsigned v) {
+#if defined(__CUDA_ARCH__)
+  return __popc(v);
+#else
+  return __builtin_popcount(v);
+#endif
+}
+FM_HD inline void star_finish(const StarCtx& s, int i, int d) {
+  const int* ring = s.ring + (size_t)i * kStarCap;
+  unsigned mask = 0;
+  int prev = ring[0];
+  for (int k = 0; k < d; k++) {
+    const int nxt = ring[k + 1 == d ? 0 : k + 1];
+    if (i < prev && i < nxt) mask |= 1u << k;
+    prev = nxt;
+  }
+  s.deg[i] = d;
+  s.own[i] = mask;
+  s.off[i] = (u64)star_popc(mask) | ((u64)(unsigned)d << 32);
+}
 
 template <bool EXACT>
 struct KStarWrapT {
@@ -252,7 +278,7 @@ struct KStarWrapT {
       if (best == p1) break;
       pk = best;
     }
-    s.deg[gi] = d;
+    star_finish(s, gi, d);
     return FM_S_OK;
   }
   // The filter kernels' form.  The wrap above visits every candidate of the block in every step -- a 32-byte
@@ -274,6 +300,12 @@ struct KStarWrapT {
   // Otherwise R grows towards what the circles found ask for and the round is repeated.
   // lst[(4 k + c) * stride]: kStarList entries of (position, wx, wy, wz), the last three float bit patterns.
 #define FM_STAR_ERR32 1.2e-6f
+#ifndef FM_STAR_PREFETCH
+#define FM_STAR_PREFETCH 1
+#endif
+#ifndef FM_STAR_CONSTB
+#define FM_STAR_CONSTB 1
+#endif
   FM_HD static float as_float(int v) {
 #if defined(__CUDA_ARCH__)
     return __int_as_float(v);
@@ -314,7 +346,12 @@ struct KStarWrapT {
           while (lo < hi && s.skey[lo] < base + (unsigned)zlo) lo++;
           while (lo < hi && s.skey[hi - 1] > base + (unsigned)zhi) hi--;
         }
-        if (lo < hi) { rng[(2 * nr) * stride] = lo; rng[(2 * nr + 1) * stride] = hi; nr++; total += hi - lo; }
+        if (lo < hi) {
+          rng[(2 * nr) * stride] = lo; rng[(2 * nr + 1) * stride] = hi; nr++; total += hi - lo;
+#if defined(__CUDA_ARCH__) && FM_STAR_PREFETCH
+          for (int q = lo & ~3; q < hi; q += 4) asm volatile("prefetch.global.L1 [%0];" ::"l"(s.spts + q));   // 128-byte lines
+#endif
+        }
       }
     }
     const double delta = 1.0e-9 * s.cell;
@@ -324,7 +361,10 @@ struct KStarWrapT {
     const double dmin = fmin(fmin(fmin(g.x - lox, hix - g.x), fmin(g.y - loy, hiy - g.y)), fmin(g.z - loz, hiz - g.z));
     const int gi = s.sidx[j];
     int* ring = s.ring + (size_t)gi * kStarCap;
-    double R2 = s.near2;
+    // first radius: the one expected to put ~7.5 candidates on the list at the LOCAL density (the block, of area
+    // ~ ((2r+1) cell)^2 on the sphere, holds `total` generators) -- 1.55 mean spacings on a uniform mesh; on a
+    // graded mesh it follows the spacing.  near2 scales it (FM_STAR_NEAR).
+    double R2 = s.near2 * 2.39 * ((2 * r + 1) * s.cell) * ((2 * r + 1) * s.cell) / (total > 1 ? total : 1);
     for (int round = 0; round < 6; round++) {
       int m = 0, over = 0, k1 = -1;
       double bd = 1.0e300;
@@ -357,6 +397,7 @@ struct KStarWrapT {
       if (round == 0 && (total < 2 || !(dmin > 0.0) || bd > dmin * dmin)) return FM_S_RADIUS;
       if (over) return FM_S_SLOW;     // more near candidates than the list holds: the full wrap
       const bool complete = (m == total - 1);
+      const float wmaxf = sqrtf((float)R2) * 1.000001f;
       bool grow = bd > R2 || k1 < 0, inbox = true;   // (not even the nearest neighbour on the list: grow)
       int unsure = 0;
       double need2 = 0.0;
@@ -399,6 +440,10 @@ struct KStarWrapT {
           const float od = vx * mx + vy * my + vz * mz;
           open += !(od > FM_STAR_ERR32 * (fabsf(vx) * max_ + fabsf(vy) * may + fabsf(vz) * maz)) ? 1 : 0;
         }
+#if FM_STAR_CONSTB
+        // one bound per step instead of one per entry: |w_i| <= |w| <= R for every entry of the list
+        const float cbn = FM_STAR_ERR32 * (nax + nay + naz) * wmaxf, cbm = FM_STAR_ERR32 * (max_ + may + maz) * wmaxf;
+#endif
 #if defined(__CUDA_ARCH__)
 #pragma unroll 4
 #endif
@@ -406,9 +451,13 @@ struct KStarWrapT {
           const float wx = as_float(lst[(4 * k + 1) * stride]), wy = as_float(lst[(4 * k + 2) * stride]),
                       wz = as_float(lst[(4 * k + 3) * stride]);
           const float det = wx * nx + wy * ny + wz * nz;
-          const float bound = FM_STAR_ERR32 * (fabsf(wx) * nax + fabsf(wy) * nay + fabsf(wz) * naz);
           const float od = wx * mx + wy * my + wz * mz;
+#if FM_STAR_CONSTB
+          const float bound = cbn, ob = cbm;
+#else
+          const float bound = FM_STAR_ERR32 * (fabsf(wx) * nax + fabsf(wy) * nay + fabsf(wz) * naz);
           const float ob = FM_STAR_ERR32 * (fabsf(wx) * max_ + fabsf(wy) * may + fabsf(wz) * maz);
+#endif
           open += (k != kk && k != kb && !(det < -bound) && !(od < -ob)) ? 1 : 0;
         }
         // fp64: the frame of the step (also needed for the circle), and the retest of what fp32 left open.  An entry
@@ -465,7 +514,7 @@ struct KStarWrapT {
       // an inconclusive proof on a list that is not yet wide enough may just be a bad guess: only the last word counts
       if (!grow && inbox && (complete || need2 <= R2)) {
         if (unsure) return FM_S_UNSURE;
-        s.deg[gi] = d;
+        star_finish(s, gi, d);
         if (s.dry && round >= 2) FM_COUNT_INC(&s.sc[FM_SC_MULTI]);
         return FM_S_OK;
       }
@@ -530,30 +579,6 @@ struct KStarExact {
 };
 
 // ------------------------------------------------------------------ from stars to rows
-FM_HD inline int star_popc(unsigned v) {
-#if defined(__CUDA_ARCH__)
-  return __popc(v);
-#else
-  return __builtin_popcount(v);
-#endif
-}
-// which triangles of its star a generator owns (it is their smallest vertex), and how many
-struct KStarOwn {
-  FM_HD static void run(const StarCtx& s, int i) {
-    const int d = s.deg[i];
-    const int* ring = s.ring + (size_t)i * kStarCap;
-    unsigned mask = 0;
-    int prev = ring[0];
-    for (int k = 0; k < d; k++) {
-      const int nxt = ring[k + 1 == d ? 0 : k + 1];
-      if (i < prev && i < nxt) mask |= 1u << k;
-      prev = nxt;
-    }
-    s.own[i] = mask;
-    s.off[i] = (u64)star_popc(mask) | ((u64)(unsigned)d << 32);
-    if (i == 0) s.off[s.n] = 0;
-  }
-};
 // position of the triangle (o, x, y) -- x followed by y -- in the star of o, or -1
 FM_HD inline int star_find(const StarCtx& s, int o, int x, int y) {
   const int d = s.deg[o];

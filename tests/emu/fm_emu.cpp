@@ -315,7 +315,7 @@ extern "C" int fme_triangulate_star(int n, const double* xyz, double kappa, int*
   s.ring = ring.data(); s.deg = deg.data(); s.own = own.data(); s.off = off.data(); s.stri = stri.data();
   s.list_exact = listE.data(); s.list_slow = listS.data(); s.sc = sc; s.row = row.data(); s.v2t = v2t.data();
   std::vector<int> rng(4 * kStarList + 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1));
-  s.near2 = 2.25 * h * h;
+  s.near2 = 1.0;
   int* lists[2] = {listA.data(), listB.data()};
   s.r = 1; s.cap_all = star_cap_all(1); s.in_idx = 1; s.out_idx = 0; s.list_out = lists[0];
   for (int j = 0; j < n; j++) KStarAllT<false>::run(s, j, rng.data(), 1);
@@ -328,7 +328,7 @@ extern "C" int fme_triangulate_star(int n, const double* xyz, double kappa, int*
   }
   for (int i = 0, m = sc[FM_SC_SLOW]; i < m; i++) KStarSlow::run(s, i, rng.data(), 1);
   for (int i = 0, m = sc[FM_SC_EXACT]; i < m; i++) KStarExact::run(s, i, rng.data(), 1);
-  for (int i = 0; i < n; i++) KStarOwn::run(s, i);
+  off[n] = 0;
   {
     u64 acc = 0;
     for (int i = 0; i <= n; i++) { u64 v = off[i]; off[i] = acc; acc += v; }
