@@ -295,11 +295,13 @@ def extra_cold(fb, p, rho, steps, peak):
     clocks = clk.stop()
     _, rows = profiled(m, lambda: m.lloyd(rho, max_iter=steps, warm=False))
     st = m.stats()
+    star = m.star_stats()
     m.close()
     n = len(p)
     per = ms / steps
     return {"mode": "cold", "value": steps / (ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": per, "clocks": clocks,
             "launches_per_step": st["launches"] / steps, "insertion_rounds_per_build": st["rounds"] / steps,
+            "builds_by_stars": star["builds"], "builds_by_insertion": star["fallbacks"],
             "roofline": {"bound": "hbm", "scope": "whole iteration", "alg_bytes_per_item": ALG_BYTES["lloyd_iteration"],
                          "items": n, "achieved": ALG_BYTES["lloyd_iteration"] * n / (per * 1e-3) / 1e9, "peak": peak,
                          "unit": "GB/s", "frac": ALG_BYTES["lloyd_iteration"] * n / (per * 1e-3) / 1e9 / peak},
@@ -322,12 +324,16 @@ def extra_m2(fb, n, kind, peak, reps=3):
     clocks = clk.stop()
     _, rows = profiled(m, lambda: m.retriangulate(warm=False))
     st = m.stats()
+    star = m.star_stats()
     m.close()
     ms = float(np.median(ts))
     ach = ALG_BYTES["delaunay"] * n / (ms * 1e-3) / 1e9
     return {"points": n, "input": "U(N,0)" if kind == "uniform" else "FIB(N)+0.2h jitter", "value": n / (ms * 1e-3) / 1e6,
             "unit": "Mpts/s", "ms": ms, "ms_all": [round(t, 3) for t in ts], "clocks": clocks, "launches": st["launches"],
             "insertion_rounds": st["rounds"], "flips": st["flips"],
+            "build": "stars (csrc/star_kernels.cuh)" if star["builds"] > 0 else
+                     "insertion levels + flips (the stars' sampling pass refused the set)" if star["fallbacks"] > 0 else
+                     "insertion levels + flips",
             "roofline": {"bound": "hbm", "scope": "whole build", "alg_bytes_per_item": ALG_BYTES["delaunay"], "items": n,
                          "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak},
             "kernels": kernel_table(rows)[:10]}

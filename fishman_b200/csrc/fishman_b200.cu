@@ -115,6 +115,7 @@ struct fm_handle {
     int G = 0;
     bool ready = false, unavailable = false;
   } star;
+  int star_skip = 0;   // cold builds left before the stars are tried again on a handle whose set the sampling pass refused
   long long n_star = 0, n_star_fallback = 0;   // cold builds by stars / attempts that fell back to the insertion build
   double star_irregular = 0.0;                  // fraction of the sampled generators the first pass did not settle cheaply
   int star_last[8] = {0};                       // the last star build: retried, exact, failed, broken, owned, degree sum, flips of the check, turned-over
@@ -804,6 +805,7 @@ static int triangulate_star(fm_handle* h) {
   const char* mode = getenv("FM_COLD_BUILD");   // read at every build: the tests switch between the two
   const bool off = mode && !strcmp(mode, "flip");
   if (off || h->n < kStarMinPoints) return 1;
+  if (h->star_skip > 0) { h->star_skip--; return 1; }   // refused a moment ago: the same generators, moved a little
   if (star_alloc(h)) return 1;
 #define S(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->cuda_failed = true; \
     h->fail("CUDA error %s at %s:%d", cudaGetErrorString(e_), __FILE__, __LINE__); return -1; } } while (0)
@@ -855,7 +857,7 @@ static int triangulate_star(fm_handle* h) {
     h->n_launch++;
     const double frac = (double)(sc0[FM_SC_RETRIED] + sc0[FM_SC_MULTI]) / ((double)sblk * FM_STAR_BLOCK);
     h->star_irregular = frac;
-    if (frac > max_frac) { h->n_star_fallback++; h->star_last[2] = -1; return 1; }
+    if (frac > max_frac) { h->n_star_fallback++; h->star_last[2] = -1; h->star_skip = 3; return 1; }
   }
   h->prof_begin();
   fm_star_all<<<(n + FM_STAR_BLOCK - 1) / FM_STAR_BLOCK, FM_STAR_BLOCK, smem(1), st>>>(s, n);
@@ -1372,7 +1374,7 @@ static int batch_begin(fm_handle* h, double tol) {
 static int cold_iteration(fm_handle* h, const fm_density* rho, double* maxdisp) {
   Readback r;
   if (triangulate_cold(h)) return 1;
-  if (circumcentres(h, false)) return 1;
+  if (!h->have_cc && circumcentres(h, false)) return 1;   // (the stars' verifying sweep has written them already)
   launch_centroid(h, rho, false);
   if (readback(h, &r, "fm_lloyd")) return 1;
   h->have_cc = false; h->have_vd = false; h->have_edges = false; h->mp.have = false;
@@ -1542,6 +1544,7 @@ extern "C" int fm_get_generators(fm_handle* h, double* x, double* y, double* z) 
   return xfer_generators(h, x, y, z, true);
 }
 extern "C" int fm_set_generators(fm_handle* h, const double* x, const double* y, const double* z) {
+  h->star_skip = 0;   // a new set of generators: the stars get their chance again
   return xfer_generators(h, (double*)x, (double*)y, (double*)z, false);
 }
 
