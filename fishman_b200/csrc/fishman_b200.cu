@@ -112,9 +112,10 @@ struct fm_handle {
     P4* spts = nullptr;
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
-    int G = 0;
+    int G = 0, Gw = 0;
     bool ready = false, unavailable = false;
   } star;
+  int star_mode = 0, star_wide_builds = 0;   // 1: the last star build needed the wide mode (irregular set)
   int star_skip = 0;   // cold builds left before the stars are tried again on a handle whose set the sampling pass refused
   long long n_star = 0, n_star_fallback = 0;   // cold builds by stars / attempts that fell back to the insertion build
   double star_irregular = 0.0;                  // fraction of the sampled generators the first pass did not settle cheaply
@@ -751,6 +752,7 @@ static int cold_finish(fm_handle* h, int rounds) {
 // the insertion build: too few points, FM_COLD_BUILD=flip, a star that did not close, an inconsistency),
 // -1 = CUDA error.  Synchronous.
 static const int kStarMinPoints = 4096;
+static const double kStarWideKappa = 2.5, kStarWideNear = 2.7;   // wide mode: cell of 2.5 spacings, ~20 expected near candidates
 static int star_alloc(fm_handle* h) {
   auto& b = h->star;
   if (b.ready) return 0;
@@ -762,6 +764,9 @@ static int star_alloc(fm_handle* h) {
   if (G > kStarMaxG) G = kStarMaxG;
   if (G < 4) { b.unavailable = true; return 1; }
   b.G = G;
+  b.Gw = (int)(2.0 / (kStarWideKappa * hh));   // the wide mode's coarser grid (irregular sets)
+  if (b.Gw > G) b.Gw = G;
+  if (b.Gw < 4) b.Gw = 4;
   size_t sort_bytes = 0, scan_bytes = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, b.key, b.skey, b.idx, b.sidx, n, 0, 32, h->stream);
   cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, b.off, b.off, n + 1, h->stream);
@@ -788,8 +793,10 @@ static int star_alloc(fm_handle* h) {
     return 1;
   }
   {  // the widest retry pass wants more than the default 48 KB of dynamic shared memory
-    const int want = (int)(sizeof(int) * (2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) + 4 * kStarList) * FM_STAR_BLOCK);
+    const int want = (int)(sizeof(int) * (2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) + 4 * kStarListWide) * FM_STAR_BLOCK);
     if (cudaFuncSetAttribute(fm_star_retry, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
+        cudaFuncSetAttribute(fm_star_all, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
+        cudaFuncSetAttribute(fm_star_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
         cudaFuncSetAttribute(fm_star_slow, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
         cudaFuncSetAttribute(fm_star_exact, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess) {
       cudaGetLastError();
@@ -810,40 +817,54 @@ static int triangulate_star(fm_handle* h) {
 #define S(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->cuda_failed = true; \
     h->fail("CUDA error %s at %s:%d", cudaGetErrorString(e_), __FILE__, __LINE__); return -1; } } while (0)
   auto& b = h->star;
-  const int n = h->n, T = 2 * n - 4, G = b.G;
+  const int n = h->n, T = 2 * n - 4;
   StarCtx s;
   memset(&s, 0, sizeof s);
-  s.n = n; s.G = G; s.half_g = 0.5 * G; s.cell = 2.0 / G;
+  s.n = n;
   s.pts = h->pts; s.key = b.key; s.idx = b.idx; s.skey = b.skey; s.sidx = b.sidx; s.spts = b.spts; s.colstart = b.colstart; s.colmid = b.colmid;
   s.ring = b.ring; s.deg = b.deg; s.own = b.own; s.off = b.off; s.stri = b.stri;
   s.list_exact = b.listE; s.list_slow = b.listS; s.sc = b.sc; s.row = h->rows; s.v2t = h->v2t;
   const int nb = (n + 255) / 256;
   cudaStream_t st = h->stream;
-  // 1. grid: keys, sort by cell, records in sorted order, column starts
-  h->prof_begin();
-  S(cudaMemsetAsync(b.sc, 0, 8 * sizeof(int), st));
-  fm_star_kernel<KStarKey><<<nb, 256, 0, st>>>(s, n);
-  int bits = 1;
-  while ((1ULL << bits) < (unsigned long long)G * G * G) bits++;
-  size_t bytes = b.tmp_bytes;
-  S(cub::DeviceRadixSort::SortPairs(b.tmp, bytes, b.key, b.skey, b.idx, b.sidx, n, 0, bits, st));
-  fm_star_kernel<KStarGather><<<nb, 256, 0, st>>>(s, n);
-  fm_star_kernel<KStarCols><<<(G * G + 1 + 255) / 256, 256, 0, st>>>(s, G * G + 1);
-  h->prof_end("star_grid", n);
-  // 2. stars: all generators with a block of radius 1, then the ones that need more / the exact predicates
   int* lists[2] = {b.listA, b.listB};
-  auto smem = [](int r) { return sizeof(int) * (2 * (2 * r + 1) * (2 * r + 1) + 4 * kStarList) * FM_STAR_BLOCK; };
+  auto smem = [&](int r) { return sizeof(int) * (2 * (2 * r + 1) * (2 * r + 1) + 4 * s.list_cap) * FM_STAR_BLOCK; };
   const size_t smem_full = sizeof(int) * 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) * FM_STAR_BLOCK;
-  {
-    static const double near_scale = getenv("FM_STAR_NEAR") ? atof(getenv("FM_STAR_NEAR")) : 1.0;
-    s.near2 = near_scale > 0.0 ? near_scale : 1.0;
-  }
-  s.r = 1; s.cap_all = star_cap_all(1); s.in_idx = 1; s.out_idx = 0; s.list_out = lists[0]; s.list_in = lists[1];
-  {  // Is this point set one the stars are good at?  1/64 of the generators (whole blocks, so that the lanes of a
-     // warp are neighbours as in the real pass) go through the first pass without recording anything: where more
-     // than a tenth of them need the full wrap, a wider block or three rounds of the near list (uniform random
-     // points do), the insertion build is the faster one.
-    static const double max_frac = getenv("FM_STAR_MAX_IRREGULAR") ? atof(getenv("FM_STAR_MAX_IRREGULAR")) : 0.10;
+  static const double near_scale = getenv("FM_STAR_NEAR") ? atof(getenv("FM_STAR_NEAR")) : 1.0;
+  static const double max_frac = getenv("FM_STAR_MAX_IRREGULAR") ? atof(getenv("FM_STAR_MAX_IRREGULAR")) : 0.10;
+  static const bool no_wide = !(getenv("FM_STAR_WIDE") && atoi(getenv("FM_STAR_WIDE")) != 0);   // measured: no faster than insertion
+  // Two settings.  Regular (lattice-like sets, relaxed meshes, graded or not): cell of 2 spacings, ~7.5 expected
+  // near candidates, 16-entry lists.  Wide (irregular sets -- uniform random points want the neighbours within
+  // ~2.3 spacings, a third of them more than 16): cell of 2.5 spacings, ~20 expected, 40-entry lists.  The wide
+  // one works (same triangles) but measures no faster than insertion + flips on uniform random points -- 14.8
+  // against 13.9 ms at 2.6M, 48.4 against 49.3 ms at 10M (profiles/r02_ab_star_wide.txt) -- so it is OFF unless
+  // FM_STAR_WIDE=1.  Which setting: 1/64 of the generators (whole blocks, so that the lanes of a warp are
+  // neighbours as in the real pass) go through the first pass without recording anything; a setting is taken
+  // when at most a tenth of them (wide: 15 %) need the full wrap, a wider block or three rounds of the near
+  // list.  A handle remembers that it needed the wide one (and tries the regular one again every fourth build:
+  // a Lloyd run makes the set regular).  Neither: insertion build.
+  bool chosen = false;
+  const int first = (h->star_mode == 1 && (h->star_wide_builds & 3) != 3 && !no_wide) ? 1 : 0;
+  for (int attempt = 0; attempt < 2 && !chosen; attempt++) {
+    const int mode = attempt == 0 ? first : 1 - first;
+    if (mode == 1 && no_wide) continue;
+    const int G = mode ? b.Gw : b.G;
+    s.G = G; s.half_g = 0.5 * G; s.cell = 2.0 / G;
+    s.list_cap = mode ? kStarListWide : kStarList;
+    s.near2 = (near_scale > 0.0 ? near_scale : 1.0) * (mode ? kStarWideNear : 1.0);
+    // 1. grid: keys, sort by cell, records in sorted order, column starts
+    h->prof_begin();
+    S(cudaMemsetAsync(b.sc, 0, 8 * sizeof(int), st));
+    fm_star_kernel<KStarKey><<<nb, 256, 0, st>>>(s, n);
+    int bits = 1;
+    while ((1ULL << bits) < (unsigned long long)G * G * G) bits++;
+    size_t bytes = b.tmp_bytes;
+    S(cub::DeviceRadixSort::SortPairs(b.tmp, bytes, b.key, b.skey, b.idx, b.sidx, n, 0, bits, st));
+    fm_star_kernel<KStarGather><<<nb, 256, 0, st>>>(s, n);
+    fm_star_kernel<KStarCols><<<(G * G + 1 + 255) / 256, 256, 0, st>>>(s, G * G + 1);
+    h->prof_end("star_grid", n);
+    h->n_launch += 5;
+    // 2. the sample
+    s.r = 1; s.in_idx = 1; s.out_idx = 0; s.list_out = lists[0]; s.list_in = lists[1];
     const int every = 64, nblk = (n + FM_STAR_BLOCK - 1) / FM_STAR_BLOCK, sblk = (nblk + every - 1) / every;
     s.dry = 1;
     h->prof_begin();
@@ -854,17 +875,22 @@ static int triangulate_star(fm_handle* h) {
     S(cudaMemcpyAsync(sc0, b.sc, sizeof sc0, cudaMemcpyDeviceToHost, st));
     S(h->sync());
     S(cudaMemsetAsync(b.sc, 0, 8 * sizeof(int), st));
-    h->n_launch++;
     const double frac = (double)(sc0[FM_SC_RETRIED] + sc0[FM_SC_MULTI]) / ((double)sblk * FM_STAR_BLOCK);
     h->star_irregular = frac;
-    if (frac > max_frac) { h->n_star_fallback++; h->star_last[2] = -1; h->star_skip = 3; return 1; }
+    if (frac <= (mode ? 1.5 * max_frac : max_frac)) {
+      chosen = true;
+      if (mode) h->star_wide_builds++; else h->star_wide_builds = 0;
+      h->star_mode = mode;
+    }
   }
+  if (!chosen) { h->n_star_fallback++; h->star_last[2] = -1; h->star_skip = 3; return 1; }
+  // 3. stars: all generators with a block of radius 1, then the ones that need more / the exact predicates
   h->prof_begin();
   fm_star_all<<<(n + FM_STAR_BLOCK - 1) / FM_STAR_BLOCK, FM_STAR_BLOCK, smem(1), st>>>(s, n);
   h->prof_end("star_wrap", n);
   h->prof_begin();
   for (int r = 2; r <= kStarMaxR; r++) {
-    s.r = r; s.cap_all = star_cap_all(r); s.in_idx = (r & 1) ? 1 : 0; s.out_idx = s.in_idx ^ 1;
+    s.r = r; s.in_idx = (r & 1) ? 1 : 0; s.out_idx = s.in_idx ^ 1;
     s.list_in = lists[s.in_idx]; s.list_out = lists[s.out_idx];
     S(cudaMemsetAsync(b.sc + s.out_idx, 0, sizeof(int), st));
     fm_star_retry<<<h->sms * (r == 2 ? 4 : 1), FM_STAR_BLOCK, smem(r), st>>>(s);   // (few generators get here: a small grid starts and ends quickly)
@@ -875,12 +901,12 @@ static int triangulate_star(fm_handle* h) {
   // 3. rows
   h->prof_begin();
   S(cudaMemsetAsync(b.off + n, 0, sizeof(u64), st));
-  bytes = b.tmp_bytes;
+  size_t bytes = b.tmp_bytes;
   S(cub::DeviceScan::ExclusiveSum(b.tmp, bytes, b.off, b.off, n + 1, st));
   fm_star_kernel<KStarSlots><<<nb, 256, 0, st>>>(s, n);
   fm_star_kernel<KStarRows><<<nb, 256, 0, st>>>(s, n);
   h->prof_end("star_rows", n);
-  h->n_launch += 12 + (kStarMaxR - 1);
+  h->n_launch += 7 + (kStarMaxR - 1);
   S(cudaGetLastError());
   int sc[8];
   u64 tot = 0;

@@ -43,9 +43,8 @@ static const int kStarMaxG = 1600;  // cells per axis: G^3 < 2^32 (32-bit cell k
 #ifndef FM_STAR_LIST
 #define FM_STAR_LIST 16
 #endif
-static const int kStarList = FM_STAR_LIST;  // near candidates per generator kept by the filter kernels (wrap_near)
-// capacity of wrap_near's flat candidate list for a block of radius r (a block holds ~ (2r+1)^2 kappa^2 generators)
-FM_HD inline int star_cap_all(int r) { return r <= 1 ? 64 : (r == 2 ? 160 : (r == 3 ? 320 : 512)); }
+static const int kStarList = FM_STAR_LIST;  // near candidates per generator kept by the filter kernels (wrap_near), regular sets
+static const int kStarListWide = 40;       // ... in the wide mode (irregular sets: uniform random points)
 enum { FM_S_OK = 0, FM_S_RADIUS = 1, FM_S_UNSURE = 2, FM_S_FAIL = 3, FM_S_SLOW = 4 };
 // slots of StarCtx::sc
 enum { FM_SC_LIST0 = 0, FM_SC_LIST1 = 1, FM_SC_EXACT = 2, FM_SC_FAIL = 3, FM_SC_BROKEN = 4, FM_SC_RETRIED = 5, FM_SC_SLOW = 6, FM_SC_MULTI = 7 };
@@ -72,7 +71,7 @@ struct StarCtx {
   int* sc;               // counters, FM_SC_*
   int r;                 // block radius of this pass (cells)
   int dry;               // sampling pass: statuses are only counted (sc[FM_SC_RETRIED] not OK, sc[FM_SC_MULTI] OK after >= 3 rounds)
-  int cap_all;           // capacity of wrap_near's flat candidate list in this pass
+  int list_cap;          // capacity of wrap_near's near list (kStarList, or kStarListWide in the wide mode)
   double near2;          // scale of the first near-list radius, squared (1 = ~7.5 expected entries)
   int in_idx, out_idx;   // which of sc[0], sc[1] counts list_in / list_out
   Row* row;
@@ -298,7 +297,7 @@ struct KStarWrapT {
   // The star is final when all its circumcircles lie inside the box AND within R of g (radius rho, through g:
   // within 2 rho of g; fp64) -- no candidate off the list and no point outside the block can be inside one.
   // Otherwise R grows towards what the circles found ask for and the round is repeated.
-  // lst[(4 k + c) * stride]: kStarList entries of (position, wx, wy, wz), the last three float bit patterns.
+  // lst[(4 k + c) * stride]: s.list_cap entries of (position, wx, wy, wz), the last three float bit patterns.
 #define FM_STAR_ERR32 1.2e-6f
 #ifndef FM_STAR_PREFETCH
 #define FM_STAR_PREFETCH 1
@@ -378,7 +377,7 @@ struct KStarWrapT {
           const double dx = Q.x - g.x, dy = Q.y - g.y, dz = Q.z - g.z;
           const double d2 = dx * dx + dy * dy + dz * dz;
           const bool other = q != j;
-          const bool in = other && d2 <= R2, room = m < kStarList;
+          const bool in = other && d2 <= R2, room = m < s.list_cap;
           const bool nearer = in && room && d2 < bd;   // (the nearest neighbour is wanted only when it is on the list)
           bd = (other && d2 < bd) ? d2 : bd;
           k1 = nearer ? m : k1;
@@ -543,7 +542,7 @@ struct KStarWrapT {
 
 // first pass: every generator, block radius 1
 template <bool EXACT>
-struct KStarAllT {   // rng: 2 (2r+1)^2 + 4 kStarList ints per thread
+struct KStarAllT {   // rng: 2 (2r+1)^2 + 4 list_cap ints per thread
   FM_HD static void run(const StarCtx& s, int j, int* rng, int stride) {
     const int st = EXACT ? KStarWrapT<true>::wrap(s, j, s.r, rng, stride)
                          : KStarWrapT<false>::wrap_near(s, j, s.r, rng, stride, rng + 2 * (2 * s.r + 1) * (2 * s.r + 1) * stride);

@@ -101,7 +101,7 @@ def rebuild_after_failed_repair(xyz_old, xyz_new, skip_bump=False):
     return tri, adj, turned.value
 
 
-def triangulate_star(xyz, kappa=1.5):
+def triangulate_star(xyz, kappa=2.0, wide=False):
     """Cold build by stars (csrc/star_kernels.cuh) on the host.  Returns (rc, tri, adj, stats): rc 0 = complete,
     2 = the product would fall back to the insertion build (stats say why)."""
     p = np.ascontiguousarray(xyz, dtype=np.float64)
@@ -111,7 +111,7 @@ def triangulate_star(xyz, kappa=1.5):
     adj = np.zeros((T, 3), np.int32)
     st = np.zeros(8, np.int32)
     ip = C.POINTER(C.c_int)
-    rc = lib().fme_triangulate_star(n, p.ctypes.data_as(C.POINTER(C.c_double)), C.c_double(kappa),
+    rc = lib().fme_triangulate_star(n, p.ctypes.data_as(C.POINTER(C.c_double)), C.c_double(kappa), 1 if wide else 0,
                                     tri.ctypes.data_as(ip), adj.ctypes.data_as(ip), st.ctypes.data_as(ip))
     if rc == 1:
         raise RuntimeError(lib().fme_last_error().decode())

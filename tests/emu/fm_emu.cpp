@@ -278,7 +278,7 @@ extern "C" int fme_rebuild_after_failed_repair(int n, const double* xyz_old, con
 // fall back to the insertion build, 1 on a usage error.
 #include "../../fishman_b200/csrc/star_kernels.cuh"
 
-extern "C" int fme_triangulate_star(int n, const double* xyz, double kappa, int* tri_out, int* adj_out, int* stats) {
+extern "C" int fme_triangulate_star(int n, const double* xyz, double kappa, int wide, int* tri_out, int* adj_out, int* stats) {
   g_err[0] = 0;
   if (n < 16) { snprintf(g_err, sizeof g_err, "need at least 16 points"); return 1; }
   const int T = 2 * n - 4;
@@ -314,14 +314,14 @@ extern "C" int fme_triangulate_star(int n, const double* xyz, double kappa, int*
   for (int c = 0; c <= G * G; c++) KStarCols::run(s, c);
   s.ring = ring.data(); s.deg = deg.data(); s.own = own.data(); s.off = off.data(); s.stri = stri.data();
   s.list_exact = listE.data(); s.list_slow = listS.data(); s.sc = sc; s.row = row.data(); s.v2t = v2t.data();
-  std::vector<int> rng(4 * kStarList + 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1));
-  s.near2 = 1.0;
+  std::vector<int> rng(4 * kStarListWide + 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1));
+  s.near2 = wide ? 2.7 : 1.0; s.list_cap = wide ? kStarListWide : kStarList;
   int* lists[2] = {listA.data(), listB.data()};
-  s.r = 1; s.cap_all = star_cap_all(1); s.in_idx = 1; s.out_idx = 0; s.list_out = lists[0];
+  s.r = 1; s.in_idx = 1; s.out_idx = 0; s.list_out = lists[0];
   for (int j = 0; j < n; j++) KStarAllT<false>::run(s, j, rng.data(), 1);
   int retried = sc[0];
   for (int r = 2; r <= kStarMaxR; r++) {
-    s.r = r; s.cap_all = star_cap_all(r); s.in_idx = (r & 1) ? 1 : 0; s.out_idx = s.in_idx ^ 1;
+    s.r = r; s.in_idx = (r & 1) ? 1 : 0; s.out_idx = s.in_idx ^ 1;
     s.list_in = lists[s.in_idx]; s.list_out = lists[s.out_idx];
     sc[s.out_idx] = 0;
     for (int i = 0, m = sc[s.in_idx]; i < m; i++) KStarRetry::run(s, i, rng.data(), 1);

@@ -207,3 +207,16 @@ def test_star_build_refuses_what_it_cannot_do():
         assert np.array_equal(_check.canonical(tri), _check.canonical(t2))
     else:
         assert rc == 2
+
+
+def test_star_build_wide_setting_on_uniform_random_points():
+    """The wide setting (40-entry near lists, first radius for ~20 expected candidates; FM_STAR_WIDE=1 in the
+    product) on what it is for: same triangles as the insertion build, and far fewer generators sent through the
+    full wrap than with the regular setting."""
+    p = points.uniform(20000, 11)
+    rc, tri, adj, st = _emu.triangulate_star(p, 2.5, wide=True)
+    assert rc == 0 and st["failed"] == 0 and st["broken"] == 0, st
+    t2, _, _ = _emu.triangulate(p)
+    assert np.array_equal(_check.canonical(tri), _check.canonical(t2))
+    rc, _, _, st_reg = _emu.triangulate_star(p, 2.0, wide=False)
+    assert rc == 0 and st["slow"] * 5 < st_reg["slow"]
