@@ -11,6 +11,9 @@ kind = sys.argv[2] if len(sys.argv) > 2 else "fib"
 p = points.uniform(n, 0) if kind == "uniform" else points.fibonacci(n, 0, 0.2)
 m = fb.Mesh.from_xyz(p)
 m.delaunay_triangulation()
+if kind.startswith("x4"):   # a graded mesh: `x4<iters>` Lloyd iterations under the 4:1 refinement density first
+    m.lloyd(fb.density_x4(), max_iter=int(kind[2:] or 200), warm=True)
+    m.retriangulate(warm=True)
 ts = []
 for _ in range(5):
     m.timer_begin(); m.retriangulate(warm=False); ts.append(m.timer_end())
