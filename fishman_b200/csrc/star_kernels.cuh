@@ -44,6 +44,7 @@ static const int kStarMaxG = 1600;  // cells per axis: G^3 < 2^32 (32-bit cell k
 #define FM_STAR_LIST 16
 #endif
 static const int kStarList = FM_STAR_LIST;  // near candidates per generator kept by the filter kernels (wrap_near), regular sets
+static const int kStarMaxCandidates = 1024;  // candidates in a block beyond which wrap_near gives up (8x: the full wrap)
 static const int kStarListWide = 40;       // ... in the wide mode (irregular sets: uniform random points)
 enum { FM_S_OK = 0, FM_S_RADIUS = 1, FM_S_UNSURE = 2, FM_S_FAIL = 3, FM_S_SLOW = 4 };
 // slots of StarCtx::sc
@@ -155,7 +156,7 @@ struct KStarWrapT {
     const int idg = (int)gq.id;
     const int ix = star_cell1(s, g.x), iy = star_cell1(s, g.y), iz = star_cell1(s, g.z);
     const int zlo = iz - r < 0 ? 0 : iz - r, zhi = iz + r >= s.G ? s.G - 1 : iz + r;
-    int nr = 0;
+    int nr = 0, total = 0;
     for (int X = ix - r; X <= ix + r; X++) {
       if (X < 0 || X >= s.G) continue;
       for (int Y = iy - r; Y <= iy + r; Y++) {
@@ -171,9 +172,10 @@ struct KStarWrapT {
           while (lo < hi && s.skey[lo] < base + (unsigned)zlo) lo++;
           while (lo < hi && s.skey[hi - 1] > base + (unsigned)zhi) hi--;
         }
-        if (lo < hi) { rng[(2 * nr) * stride] = lo; rng[(2 * nr + 1) * stride] = hi; nr++; }
+        if (lo < hi) { rng[(2 * nr) * stride] = lo; rng[(2 * nr + 1) * stride] = hi; nr++; total += hi - lo; }
       }
     }
+    if (total > 8 * kStarMaxCandidates) return FM_S_FAIL;   // thousands of generators in a few cells: a cluster, the insertion build's business
     // the nearest candidate: a Delaunay neighbour (the circle on the diameter g p1 is empty), provided
     // it lies within the distance the block covers completely
     double bd = 1.0e300;
@@ -305,6 +307,9 @@ struct KStarWrapT {
 #ifndef FM_STAR_CONSTB
 #define FM_STAR_CONSTB 1
 #endif
+#ifndef FM_STAR_PIPE
+#define FM_STAR_PIPE 1   // A/B at 2.6M: star_wrap 2.40 -> 2.26 ms
+#endif
   FM_HD static float as_float(int v) {
 #if defined(__CUDA_ARCH__)
     return __int_as_float(v);
@@ -353,6 +358,7 @@ struct KStarWrapT {
         }
       }
     }
+    if (total > kStarMaxCandidates) return FM_S_SLOW;   // a clustered cell: not for the list form (and never in a loop of six rounds)
     const double delta = 1.0e-9 * s.cell;
     const double lox = (ix - r) * s.cell - 1.0 + delta, hix = (ix + r + 1) * s.cell - 1.0 - delta;
     const double loy = (iy - r) * s.cell - 1.0 + delta, hiy = (iy + r + 1) * s.cell - 1.0 - delta;
@@ -369,11 +375,23 @@ struct KStarWrapT {
       double bd = 1.0e300;
       {
         int a_ = 0, q = nr ? rng[0] : 0, e_ = nr ? rng[stride] : 0;
+#if FM_STAR_PIPE
+        // the next candidate's record is requested before this one is worked on
+        int qn = q;
+        P4 Qn = total > 0 ? s.spts[qn] : gq;
+        for (int k = 0; k < total; k++) {
+          const P4 Q = Qn;
+          q = qn;
+          qn++;
+          if (qn == e_ && a_ + 1 < nr) { a_++; qn = rng[(2 * a_) * stride]; e_ = rng[(2 * a_ + 1) * stride]; }
+          if (k + 1 < total) Qn = s.spts[qn];
+#else
 #if defined(__CUDA_ARCH__)
 #pragma unroll 4
 #endif
         for (int k = 0; k < total; k++) {
           const P4 Q = s.spts[q];
+#endif
           const double dx = Q.x - g.x, dy = Q.y - g.y, dz = Q.z - g.z;
           const double d2 = dx * dx + dy * dy + dz * dz;
           const bool other = q != j;
@@ -389,8 +407,10 @@ struct KStarWrapT {
           }
           over |= (in && !room) ? 1 : 0;
           m += (in && room) ? 1 : 0;
+#if !FM_STAR_PIPE
           q++;
           if (q == e_ && a_ + 1 < nr) { a_++; q = rng[(2 * a_) * stride]; e_ = rng[(2 * a_ + 1) * stride]; }
+#endif
         }
       }
       if (round == 0 && (total < 2 || !(dmin > 0.0) || bd > dmin * dmin)) return FM_S_RADIUS;
