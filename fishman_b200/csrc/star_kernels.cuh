@@ -307,6 +307,9 @@ struct KStarWrapT {
 #ifndef FM_STAR_CONSTB
 #define FM_STAR_CONSTB 1
 #endif
+#ifndef FM_STAR_TRIM
+#define FM_STAR_TRIM 0   // A/B at 2.6M: counting the keys outside the wanted cells with 12 independent loads, star_wrap 2.26 -> 2.40 ms
+#endif
 #ifndef FM_STAR_PIPE
 #define FM_STAR_PIPE 1   // A/B at 2.6M: star_wrap 2.40 -> 2.26 ms
 #endif
@@ -347,8 +350,25 @@ struct KStarWrapT {
           lo = star_lower(s.skey, lo, hi, base + (unsigned)zlo);
           hi = star_lower(s.skey, lo, hi, base + (unsigned)zhi + 1u);
         } else {
+#if FM_STAR_TRIM
+          // the keys are sorted: how many lie below / above the wanted cells -- twelve independent loads instead of
+          // a walk in from both ends, one dependent load per step
+          int below = 0, above = 0;
+          const unsigned klo = base + (unsigned)zlo, khi = base + (unsigned)zhi;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+          for (int t = 0; t < 12; t++) {
+            const bool valid = lo + t < hi;
+            const unsigned key = valid ? s.skey[lo + t] : klo;
+            below += (valid && key < klo) ? 1 : 0;
+            above += (valid && key > khi) ? 1 : 0;
+          }
+          lo += below; hi -= above;
+#else
           while (lo < hi && s.skey[lo] < base + (unsigned)zlo) lo++;
           while (lo < hi && s.skey[hi - 1] > base + (unsigned)zhi) hi--;
+#endif
         }
         if (lo < hi) {
           rng[(2 * nr) * stride] = lo; rng[(2 * nr + 1) * stride] = hi; nr++; total += hi - lo;
