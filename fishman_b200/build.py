@@ -5,9 +5,9 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libfishman_b200.so")
 SRC = os.path.join(HERE, "csrc", "fishman_b200.cu")
-DEPS = [os.path.join(HERE, "csrc", f) for f in
-        ("fishman_b200.cu", "predicates.cuh", "sos_tables.inc", "dt_kernels.cuh", "dt_driver.h",
-         "vd_kernels.cuh", "launch_kernels.cuh", "mpas_kernels.cuh")] + [os.path.join(HERE, "..", "include", "fishman_b200.h")]
+CSRC = os.path.join(HERE, "csrc")
+# every file under csrc/ (a list by name once missed a new header: the library stayed stale)
+DEPS = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(HERE, "..", "include", "fishman_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 
