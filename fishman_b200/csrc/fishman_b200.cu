@@ -793,11 +793,12 @@ static int star_alloc(fm_handle* h) {
     return 1;
   }
   {  // the widest retry pass wants more than the default 48 KB of dynamic shared memory
-    const int want = (int)(sizeof(int) * (2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) + 4 * kStarListWide) * FM_STAR_BLOCK);
+    const int want = (int)(sizeof(int) * (2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) + 4 * kStarListLong) * FM_STAR_BLOCK);
     if (cudaFuncSetAttribute(fm_star_retry, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
         cudaFuncSetAttribute(fm_star_all, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
         cudaFuncSetAttribute(fm_star_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
         cudaFuncSetAttribute(fm_star_slow, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
+        cudaFuncSetAttribute(fm_star_slow_near, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess ||
         cudaFuncSetAttribute(fm_star_exact, cudaFuncAttributeMaxDynamicSharedMemorySize, want) != cudaSuccess) {
       cudaGetLastError();
       b.unavailable = true;
@@ -895,7 +896,14 @@ static int triangulate_star(fm_handle* h) {
     S(cudaMemsetAsync(b.sc + s.out_idx, 0, sizeof(int), st));
     fm_star_retry<<<h->sms * (r == 2 ? 4 : 1), FM_STAR_BLOCK, smem(r), st>>>(s);   // (few generators get here: a small grid starts and ends quickly)
   }
-  fm_star_slow<<<h->sms * 2, FM_STAR_BLOCK, smem_full, st>>>(s);
+  {  // the overflowed lists: the list form again with long lists, then (list A, counted in sc[0]) the full wrap
+    StarCtx sl = s;
+    sl.list_cap = kStarListLong; sl.list_in = lists[0];
+    S(cudaMemsetAsync(b.sc + FM_SC_LIST0, 0, sizeof(int), st));
+    const size_t smem_long = sizeof(int) * (2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) + 4 * kStarListLong) * FM_STAR_BLOCK;
+    fm_star_slow_near<<<h->sms * 4, FM_STAR_BLOCK, smem_long, st>>>(sl);
+    fm_star_slow<<<h->sms * 2, FM_STAR_BLOCK, smem_full, st>>>(sl);
+  }
   fm_star_exact<<<h->sms * 2, FM_STAR_BLOCK, smem_full, st>>>(s);
   h->prof_end("star_retry", 0);
   // 3. rows
@@ -906,7 +914,7 @@ static int triangulate_star(fm_handle* h) {
   fm_star_kernel<KStarSlots><<<nb, 256, 0, st>>>(s, n);
   fm_star_kernel<KStarRows><<<nb, 256, 0, st>>>(s, n);
   h->prof_end("star_rows", n);
-  h->n_launch += 7 + (kStarMaxR - 1);
+  h->n_launch += 8 + (kStarMaxR - 1);
   S(cudaGetLastError());
   int sc[8];
   u64 tot = 0;

@@ -230,9 +230,15 @@ __global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_retry(StarCtx s) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
     KStarRetry::run(s, i, star_smem + threadIdx.x, blockDim.x);
 }
-__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_slow(StarCtx s) {
+__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_slow_near(StarCtx s) {
   extern __shared__ int star_smem[];
   const int m = s.sc[FM_SC_SLOW];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
+    KStarSlowNear::run(s, i, star_smem + threadIdx.x, blockDim.x);
+}
+__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_slow(StarCtx s) {
+  extern __shared__ int star_smem[];
+  const int m = s.sc[FM_SC_LIST0];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
     KStarSlow::run(s, i, star_smem + threadIdx.x, blockDim.x);
 }

@@ -45,6 +45,7 @@ static const int kStarMaxG = 1600;  // cells per axis: G^3 < 2^32 (32-bit cell k
 #endif
 static const int kStarList = FM_STAR_LIST;  // near candidates per generator kept by the filter kernels (wrap_near), regular sets
 static const int kStarMaxCandidates = 1024;  // candidates in a block beyond which wrap_near gives up (8x: the full wrap)
+static const int kStarListLong = 96;        // ... for the generators whose list overflowed (KStarSlowNear)
 static const int kStarListWide = 40;       // ... in the wide mode (irregular sets: uniform random points)
 enum { FM_S_OK = 0, FM_S_RADIUS = 1, FM_S_UNSURE = 2, FM_S_FAIL = 3, FM_S_SLOW = 4 };
 // slots of StarCtx::sc
@@ -559,6 +560,7 @@ struct KStarWrapT {
       }
       if (complete) return unsure ? FM_S_UNSURE : FM_S_RADIUS;   // every candidate of the block was on the list
       R2 = need2 < 1.3 * R2 ? 1.3 * R2 : (need2 > 2.0 * R2 ? 2.0 * R2 : need2);   // partial stars overestimate: grow gently
+      if (round == 4) R2 = 1.0e300;   // last round: every candidate of the block, if the list holds them
     }
     return FM_S_SLOW;
   }
@@ -597,10 +599,24 @@ struct KStarRetry {
                                                                  rng + 2 * (2 * s.r + 1) * (2 * s.r + 1) * stride));
   }
 };
-// the generators whose near list overflowed: the full wrap with the filters, widening the block as needed
-struct KStarSlow {
+// the generators whose near list overflowed, first attempt: the same list form with a long list (kStarListLong
+// entries; few generators get here, so the shared memory does not matter), widening the block as needed.  What
+// overflows even that goes on list_in (counted in sc[FM_SC_LIST0]) for the full wrap.
+struct KStarSlowNear {
   FM_HD static void run(const StarCtx& s, int i, int* rng, int stride) {
     const int j = s.list_slow[i];
+    int st = FM_S_RADIUS;
+    for (int r = 1; r <= kStarMaxR && st == FM_S_RADIUS; r++)
+      st = KStarWrapT<false>::wrap_near(s, j, r, rng, stride, rng + 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1) * stride);
+    if (st == FM_S_UNSURE) s.list_exact[FM_COUNT_INC(&s.sc[FM_SC_EXACT])] = j;
+    else if (st == FM_S_SLOW) s.list_in[FM_COUNT_INC(&s.sc[FM_SC_LIST0])] = j;
+    else if (st != FM_S_OK) FM_COUNT_INC(&s.sc[FM_SC_FAIL]);
+  }
+};
+// ... second attempt: the full wrap with the filters (list_in, sc[FM_SC_LIST0])
+struct KStarSlow {
+  FM_HD static void run(const StarCtx& s, int i, int* rng, int stride) {
+    const int j = s.list_in[i];
     int st = FM_S_RADIUS;
     for (int r = 1; r <= kStarMaxR && st == FM_S_RADIUS; r++) st = KStarWrapT<false>::wrap(s, j, r, rng, stride);
     if (st == FM_S_UNSURE) s.list_exact[FM_COUNT_INC(&s.sc[FM_SC_EXACT])] = j;

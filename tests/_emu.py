@@ -109,11 +109,11 @@ def triangulate_star(xyz, kappa=2.0, wide=False):
     T = 2 * n - 4
     tri = np.zeros((T, 3), np.int32)
     adj = np.zeros((T, 3), np.int32)
-    st = np.zeros(8, np.int32)
+    st = np.zeros(12, np.int32)
     ip = C.POINTER(C.c_int)
     rc = lib().fme_triangulate_star(n, p.ctypes.data_as(C.POINTER(C.c_double)), C.c_double(kappa), 1 if wide else 0,
                                     tri.ctypes.data_as(ip), adj.ctypes.data_as(ip), st.ctypes.data_as(ip))
     if rc == 1:
         raise RuntimeError(lib().fme_last_error().decode())
-    names = ("retried", "exact", "failed", "broken", "owned", "degree_sum", "cells_per_axis", "slow")
-    return rc, tri, adj, dict(zip(names, (int(v) for v in st[:8])))
+    names = ("retried", "exact", "failed", "broken", "owned", "degree_sum", "cells_per_axis", "slow", "full_wrap")
+    return rc, tri, adj, dict(zip(names, (int(v) for v in st[:9])))

@@ -326,7 +326,15 @@ extern "C" int fme_triangulate_star(int n, const double* xyz, double kappa, int 
     sc[s.out_idx] = 0;
     for (int i = 0, m = sc[s.in_idx]; i < m; i++) KStarRetry::run(s, i, rng.data(), 1);
   }
-  for (int i = 0, m = sc[FM_SC_SLOW]; i < m; i++) KStarSlow::run(s, i, rng.data(), 1);
+  {
+    StarCtx sl = s;
+    sl.list_cap = kStarListLong; sl.list_in = lists[0];
+    sc[FM_SC_LIST0] = 0;
+    std::vector<int> rl(4 * kStarListLong + 2 * (2 * kStarMaxR + 1) * (2 * kStarMaxR + 1));
+    for (int i = 0, m = sc[FM_SC_SLOW]; i < m; i++) KStarSlowNear::run(sl, i, rl.data(), 1);
+    if (stats) stats[8] = sc[FM_SC_LIST0];
+    for (int i = 0, m = sc[FM_SC_LIST0]; i < m; i++) KStarSlow::run(sl, i, rng.data(), 1);
+  }
   for (int i = 0, m = sc[FM_SC_EXACT]; i < m; i++) KStarExact::run(s, i, rng.data(), 1);
   off[n] = 0;
   {
