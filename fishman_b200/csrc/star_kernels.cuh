@@ -6,23 +6,25 @@
 // DV:845-882); the insertion-level build of dt_driver.h does the same in parallel rounds and is
 // bound by the latency of ~3 flips per point of ~14 scattered accesses each in ~60 sub-rounds of
 // four launches.  For a point set whose spacing does not vary wildly (the meshes this code is
-// for: Fibonacci / icosahedral / relaxed SCVT generators, uniform random points) every
+// for: Fibonacci / icosahedral / relaxed SCVT generators, graded or not) every
 // generator's STAR -- its Delaunay neighbours in counter-clockwise order -- can be found
 // independently from the few dozen points around it:
 //
-//   1. bin the generators into a uniform 3-D grid over [-1,1]^3 (cell ~ 1.5 mean spacings; only the
-//      cells the sphere passes through are occupied), sort by cell, table of column starts;
-//   2. one thread per generator g: the candidates are the points of the (2r+1)^3 block of cells
+//   1. bin the generators into a uniform 3-D grid over [-1,1]^3 (cell = 2 mean spacings; only the cells the
+//      sphere passes through are occupied), sort by cell, tables of column starts / column halves;
+//   2. one thread per generator g, in sorted order: the candidates are the points of the (2r+1)^3 block of cells
 //      around g's cell, which holds EVERY point within r cells of g.  The nearest candidate p1 is a
 //      Delaunay neighbour; from the Delaunay edge (g, p_k) the next neighbour p_k+1 is the
 //      candidate q on the left of g -> p_k whose circle (g, p_k, q) holds no other candidate on the
-//      left (gift wrapping, exact: the same orient / incircle predicates with the same
-//      simulation-of-simplicity tie-break as the flips, filter first, exact kernel for the
-//      generators with an inconclusive filter) until the ring closes at p1.  The star is final when
-//      every circumcircle found lies inside the searched block (its diameter <= r cells): no
-//      unseen point can be inside.  Otherwise the generator is retried with r + 1 (compact list);
-//   3. triangle (g, p_k, p_k+1) belongs to its smallest vertex: mask + count per generator, one
-//      scan gives the slots -- already in the order sort_triangles would produce -- and the rows
+//      left (gift wrapping) until the ring closes at p1.  KStarWrapT::wrap does exactly that over all candidates
+//      with the filtered (or, EXACT, the full: expansion arithmetic + simulation of simplicity, the flips' own)
+//      predicates; KStarWrapT::wrap_near, the form nearly every generator goes through, does it on a short list
+//      of the candidates near g kept in shared memory as fp32 offsets: the next neighbour is guessed in fp32 and
+//      the guess certified in fp32, then fp64, then -- rarely -- by the exact kernel (see there).  The star is
+//      final when every circumcircle found lies inside the searched block: no unseen point can be inside.
+//      Otherwise: a longer list, a wider block (r + 1, compact retry lists), the full wrap, the exact kernel;
+//   3. triangle (g, p_k, p_k+1) belongs to its smallest vertex: mask + count per generator (written by the wrap),
+//      one scan gives the slots -- already in the order sort_triangles would produce -- and the rows
 //      (vertices + adjacency) are written by looking the neighbours up in the rings.
 //
 // The result is checked, not trusted: every triangle of every star must be found in the star of
@@ -30,7 +32,8 @@
 // Euler characteristic 2), and the warm sweep (orientation + local Delaunay test of every edge)
 // then runs over the rows; anything else -- a star that does not close within kStarMaxR cells or
 // kStarCap neighbours (lat-lon grids at the poles, clustered points) -- and the build falls back to
-// the insertion-level path.  Both give the Delaunay triangulation of the SoS-perturbed points,
+// the insertion-level path; a sampling pass sends sets the stars are slow at (uniform random points) there
+// before any work is done.  Both give the Delaunay triangulation of the SoS-perturbed points,
 // which is unique: same triangles, bit for bit.
 #pragma once
 #include "dt_kernels.cuh"
