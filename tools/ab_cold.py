@@ -8,7 +8,7 @@ from fishman_b200 import points
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 2621442
 kind = sys.argv[2] if len(sys.argv) > 2 else "fib"
-p = points.uniform(n, 0) if kind == "uniform" else points.fibonacci(n, 0, 0.2)
+p = points.uniform(n, 0) if kind == "uniform" else points.fibonacci(n, 0, float(kind[4:]) if kind.startswith("fibj") else 0.2)
 m = fb.Mesh.from_xyz(p)
 m.delaunay_triangulation()
 if kind.startswith("x4"):   # a graded mesh: `x4<iters>` Lloyd iterations under the 4:1 refinement density first
