@@ -213,7 +213,11 @@ __global__ void __launch_bounds__(256) fm_star_kernel(StarCtx s, int n) {
 #ifndef FM_STAR_BLOCK
 #define FM_STAR_BLOCK 64
 #endif
-__global__ void __launch_bounds__(FM_STAR_BLOCK) fm_star_all(StarCtx s, int n) {
+#ifndef FM_STAR_MINB
+#define FM_STAR_MINB 10   // resident blocks per SM the register budget is set for: 96 registers (20 bytes of spill).  A/B at
+                          // 2.6M, star_wrap: 8 blocks (122 registers) 2.21 ms, 10: 2.09, 12 (80 registers, 124 bytes spilled): 2.31
+#endif
+__global__ void __launch_bounds__(FM_STAR_BLOCK, FM_STAR_MINB) fm_star_all(StarCtx s, int n) {
   extern __shared__ int star_smem[];
   int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j < n) KStarAllT<false>::run(s, j, star_smem + threadIdx.x, blockDim.x);
