@@ -56,3 +56,13 @@ def test_sass_is_sm100a_only():
     out = subprocess.check_output(["cuobjdump", "--list-elf", build.LIB], text=True)
     archs = set(re.findall(r"sm_\d+a?", out))
     assert archs == {"sm_100a"}, archs
+
+
+def test_build_staleness_check_covers_every_source():
+    """The in-tree library is rebuilt when ANY file under csrc/ changes (a list by name once missed a new header
+    and the GPU runs silently used a stale library)."""
+    from fishman_b200 import build
+    csrc = os.path.join(ROOT, "fishman_b200", "csrc")
+    deps = {os.path.realpath(d) for d in build.DEPS}
+    for f in os.listdir(csrc):
+        assert os.path.realpath(os.path.join(csrc, f)) in deps, f
