@@ -266,7 +266,7 @@ class Mesh:
         import numpy as np
         out = np.zeros(10, np.int64)
         self._chk(_lib.lib().fm_star_stats(self._h, out.ctypes.data_as(C.POINTER(C.c_int64))))
-        names = ("builds", "fallbacks", "reserved", "exact", "failed", "broken", "triangles", "degree_sum", "check_flips",
+        names = ("builds", "fallbacks", "overflowed", "exact", "failed", "broken", "triangles", "degree_sum", "check_flips",
                  "check_turned")
         return dict(zip(names, (int(v) for v in out)))
 

@@ -212,14 +212,15 @@ int fm_host_free(void* p);
 int fm_timer_begin(fm_handle* h);
 int fm_timer_end(fm_handle* h, double* ms);
 /* stats[0..7]: insertion rounds, flip sub-rounds, flips, largest flip queue, kernel
- * launches since the last fm_stats_reset, cold rebuilds, warm repairs, reserved */
+ * launches since the last fm_stats_reset, cold rebuilds, warm repairs, cold builds made by stars (fm_star_stats) */
 int fm_stats(const fm_handle* h, int64_t* stats);
 int fm_stats_reset(fm_handle* h);
 /* The cold build "by stars" (every generator's Delaunay neighbours found independently from the points
  * around it, csrc/star_kernels.cuh; replaces the insertion + flip rounds of DV:255-321 / DV:845-882 for
  * well-spaced generators and falls back to them otherwise; FM_COLD_BUILD=flip switches it off).
  * out[0] builds completed that way since the last fm_stats_reset, out[1] attempts that fell back, then of
- * the last attempt: out[2] reserved, out[3] generators redone with the exact predicates, out[4] stars that
+ * the last attempt: out[2] generators whose near list overflowed (second attempt with long lists), out[3] generators redone with
+ * the exact predicates, out[4] stars that
  * did not close, out[5] triangles missing from their owner's star, out[6] triangles, out[7] sum of the
  * degrees, out[8] flips and out[9] turned-over triangles found by the verifying sweep (both must be 0). */
 int fm_star_stats(const fm_handle* h, int64_t* out);
