@@ -24,6 +24,7 @@ module fishman_gpu_c
   public :: fm_lloyd, fm_lloyd_local, fm_generator_block, fm_peer_handle, fm_peer_attach
   public :: fm_get_generators, fm_set_generators, fm_density_eval
   public :: fm_quality_stats, fm_quality, fm_block_ids, fm_get_generators_block, fm_set_generators_block, fm_fp64_peak
+  public :: fm_quality_static, fm_star_stats
   public :: fm_error_message
 
   ! typedef struct fm_density { int32_t kind; double cx, cy, cz, beta, alpha, gamma; }
@@ -231,6 +232,21 @@ module fishman_gpu_c
       type(fm_density), intent(in) :: rho
       type(fm_quality_stats), intent(out) :: q
     end function fm_quality
+
+    ! fm_quality under the uniform density without any device allocation (no counterpart in the reference; scratch in
+    ! a static device array of the library, at most 4,194,304 generators, the triangulation must be current)
+    integer(c_int) function fm_quality_static(h, q) bind(C, name='fm_quality_static')
+      import :: c_int, c_ptr, fm_quality_stats
+      type(c_ptr), value :: h
+      type(fm_quality_stats), intent(out) :: q
+    end function fm_quality_static
+
+    ! how the last cold build was made (by stars or by insertion + flips): ten 64-bit words, include/fishman_b200.h
+    integer(c_int) function fm_star_stats(h, out) bind(C, name='fm_star_stats')
+      import :: c_int, c_int64_t, c_ptr
+      type(c_ptr), value :: h
+      integer(c_int64_t), intent(out) :: out(10)
+    end function fm_star_stats
 
     ! one rank's block of a sharded mesh (fm_create_dist): ids, download, upload
     integer(c_int) function fm_block_ids(h, ids) bind(C, name='fm_block_ids')
