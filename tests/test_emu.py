@@ -220,3 +220,50 @@ def test_star_build_wide_setting_on_uniform_random_points():
     assert np.array_equal(_check.canonical(tri), _check.canonical(t2))
     rc, _, _, st_reg = _emu.triangulate_star(p, 2.0, wide=False)
     assert rc == 0 and st["slow"] * 5 < st_reg["slow"]
+
+
+def _cubesphere(m):
+    t = np.linspace(-1, 1, m)
+    a, b = (v.ravel() for v in np.meshgrid(t, t, indexing="ij"))
+    o = np.ones_like(a)
+    p = np.concatenate([np.stack(f, 1) for f in ((o, a, b), (-o, a, b), (a, o, b), (a, -o, b), (a, b, o), (a, b, -o))])
+    p /= np.linalg.norm(p, axis=1)[:, None]
+    return np.unique(np.round(p, 14), axis=0)
+
+
+def _latlon_band(nlat):
+    """a lat-lon grid between +-69 degrees (rows of cocircular points, cocircular quads everywhere) + two random caps"""
+    lat = np.linspace(-1.2, 1.2, nlat)
+    lon = np.arange(2 * nlat) / (2 * nlat) * 2 * np.pi
+    la, lo = np.meshgrid(lat, lon, indexing="ij")
+    p = np.stack([np.cos(la) * np.cos(lo), np.cos(la) * np.sin(lo), np.sin(la)], -1).reshape(-1, 3)
+    cap = points.uniform(400, 1) * 0.25 + np.array([0, 0, 1.0])
+    cap /= np.linalg.norm(cap, axis=1)[:, None]
+    return np.concatenate([p, cap, cap * np.array([1, 1, -1.0])])
+
+
+@pytest.mark.parametrize("name", ["cubesphere", "latlon_band", "fib_jitter_0.5"])
+def test_star_build_on_degenerate_and_irregular_sets(name):
+    """Cocircular quads everywhere (cube-sphere grid, lat-lon band: most generators end in the exact kernel, whose
+    SoS tie-break is the flips') and a strongly jittered lattice (hundreds of overflowing near lists: second
+    attempt with long lists): the same triangles as the insertion build."""
+    p = {"cubesphere": lambda: _cubesphere(40), "latlon_band": lambda: _latlon_band(64),
+         "fib_jitter_0.5": lambda: points.fibonacci(12000, 5, 0.5)}[name]()
+    rc, tri, adj, st = _emu.triangulate_star(p, 2.0)
+    assert rc == 0 and st["failed"] == 0 and st["broken"] == 0, st
+    if name == "fib_jitter_0.5":
+        assert st["slow"] > 0 and st["exact"] == 0
+    else:
+        assert st["exact"] > 100
+    _check.check_triangulation(p, tri, adj)
+    t2, _, _ = _emu.triangulate(p)
+    assert np.array_equal(_check.canonical(tri), _check.canonical(t2))
+
+
+def test_star_build_refuses_near_duplicate_pairs():
+    """Pairs of generators 1e-9 apart: slivers whose normals cannot be trusted -- refused (rc 2), not guessed."""
+    p = points.fibonacci(6000, 3)
+    q = p[::7] + 1e-9 * np.random.default_rng(0).standard_normal(p[::7].shape)
+    q /= np.linalg.norm(q, axis=1)[:, None]
+    rc, _, _, st = _emu.triangulate_star(np.concatenate([p, q]), 2.0)
+    assert rc == 2 and st["failed"] > 0
